@@ -1,0 +1,149 @@
+/*
+ * pir_b200.h — C ABI of the B200-native server-side answer path for the two-server DPF PIR of
+ * mvmcconnell/pir.  This is the drop-in boundary: everything a cgo (or ctypes / C++) binding of the
+ * reference's hot path needs, with plain pointers and sizes only.
+ *
+ * Reference interfaces replaced (paths relative to the reference tree):
+ *   dpf.ServerInitialize                      dpf/server.go:16-46   -> key schedule happens inside every call
+ *   (*Dpf).Evaluate2P                         dpf/server.go:55-101  -> pir_dpf_eval_points
+ *   (*Database).ExpandSharedQuery             db.go:110-174         -> pir_expand_bits
+ *   (*Database).PrivateSecretSharedQueryWithExpandedBits db.go:75-107 -> pir_answer_with_bits
+ *   (*Database).PrivateSecretSharedQuery      db.go:68-72           -> pir_answer / pir_answer_batch
+ *   XorSlots / Recover                        slot.go:19-30, query.go:278-297 -> pir_xor_combine (host)
+ *   Database{Slots []*Slot}                   db.go:22-26           -> pir_db handle (flat device copy)
+ *   Database.SetKeywords                      db.go:392-394         -> pir_db_set_keywords
+ *   QueryShare + dpf.Key2P + dpf.PrfKey       query.go:14-22, dpf/common.go:13-35 -> pir_query POD
+ *
+ * Conventions
+ *   - every function returns PIR_OK (0) or a negative pir_status; pir_last_error() gives a
+ *     thread-local human-readable message for the last failure on the calling thread.
+ *   - the library never frees or keeps caller memory; outputs go to caller-allocated buffers.
+ *   - a pir_db handle is bound to ONE CUDA device and owns a flat copy of (a shard of) the slots.
+ *     Calls on one handle are serialised by an internal mutex; different handles are independent.
+ *   - there is NO CPU fallback: without a usable CUDA device every compute entry point fails with
+ *     PIR_ERR_CUDA.
+ */
+#ifndef PIR_B200_H
+#define PIR_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PIR_B200_ABI_VERSION 1
+#define PIR_MAX_NUM_BITS 64   /* dpf tests use 64-bit domains (dpf/dpf_test.go:73-107) */
+#define PIR_CW_BYTES 18       /* sCW[16] || tLCW || tRCW  (dpf/client.go:83-84,118-125) */
+#define PIR_NUM_PRF_KEYS 4    /* initPRFLen (dpf/common.go:10); only keys 0..2 are used by 2-party eval */
+
+typedef enum pir_status {
+    PIR_OK = 0,
+    PIR_ERR_BAD_ARG = -1,     /* null pointer, zero size, group size not dividing a shard, ... */
+    PIR_ERR_BAD_KEY = -2,     /* num_bits out of range, t_init not 0/1, share_number > 1 ... */
+    PIR_ERR_CUDA = -3,        /* any CUDA runtime failure (message carries cudaGetErrorString) */
+    PIR_ERR_OOM = -4,         /* host or device allocation failed */
+    PIR_ERR_UNSUPPORTED = -5  /* multi-party (>2 shares) keys: unreachable in the reference too
+                                 (dpf/client.go:152-156 panics "not implemented") */
+} pir_status;
+
+/*
+ * One server's share of a query: QueryShare (query.go:14-22) with its Key2P (dpf/common.go:30-35)
+ * and the four shipped PRF keys (dpf/common.go:13-15) flattened into a POD.  160+ bytes of header
+ * followed by 64 fixed correction-word slots, of which the first num_bits are meaningful.  This is
+ * also the wire format the reference lacks.
+ */
+typedef struct pir_query {
+    uint8_t  prf_keys[PIR_NUM_PRF_KEYS][16]; /* QueryShare.PrfKeys[i].Bytes                         */
+    uint8_t  s_init[16];                     /* Key2P.SInit                                         */
+    uint8_t  t_init;                         /* Key2P.TInit, 0 or 1                                 */
+    uint8_t  share_number;                   /* QueryShare.ShareNumber, 0 or 1                      */
+    uint8_t  is_keyword;                     /* QueryShare.IsKeywordBased                           */
+    uint8_t  is_two_party;                   /* QueryShare.IsTwoParty, must be 1                    */
+    uint32_t num_bits;                       /* len(Key2P.CW); informational for pir_answer*, which
+                                                recompute it like db.go:117-121 and reject a mismatch */
+    int64_t  final_cw;                       /* Key2P.FinalCW (Go int, wrapping int64)              */
+    uint32_t group_size;                     /* QueryShare.GroupSize                                */
+    uint32_t reserved;                       /* must be 0                                           */
+    uint8_t  cw[PIR_MAX_NUM_BITS][PIR_CW_BYTES]; /* Key2P.CW[i]                                     */
+} pir_query;
+
+typedef struct pir_db pir_db; /* opaque */
+
+/* ---- library / device ------------------------------------------------------------------------ */
+int         pir_abi_version(void);
+const char* pir_last_error(void);
+/* Number of visible CUDA devices (0 when there is none); never fails. */
+int         pir_device_count(void);
+
+/* ---- database handle (replaces Database{DBMetadata, Slots, Keywords}, db.go:15-26) ------------ */
+/*
+ * Create a handle on `device` for the slots [slot_begin, slot_begin+slot_count) of a logical
+ * database of db_size slots x slot_bytes bytes.  A single-GPU server passes slot_begin = 0,
+ * slot_count = db_size.  A row-sharded multi-GPU server creates one handle per GPU; a query with
+ * group size W then needs slot_begin % W == 0 and (slot_count % W == 0 or the shard is the last).
+ * Slots are stored flat with a pitch of slot_bytes rounded up to 16 (pir_db_slot_pitch).
+ */
+int pir_db_create(int device, uint64_t db_size, uint32_t slot_bytes,
+                  uint64_t slot_begin, uint64_t slot_count, pir_db** out);
+int pir_db_destroy(pir_db* db);
+/* Copy n_slots densely packed slots (n_slots*slot_bytes host bytes) into global slots
+ * [slot_index, slot_index+n_slots), which must lie inside the shard. */
+int pir_db_upload(pir_db* db, uint64_t slot_index, const void* host_slots, uint64_t n_slots);
+/* Read slots back (testing / Database round trips). */
+int pir_db_download(pir_db* db, uint64_t slot_index, void* host_slots, uint64_t n_slots);
+/* Fill the shard on the device with the seeded synthetic generator of DESIGN.md ("pir_synth"):
+ * byte j of slot i is a pure function of (seed, i, j), identical to oracle/pir_oracle.c orc_synth_fill. */
+int pir_db_fill_synthetic(pir_db* db, uint64_t seed);
+/* Keywords for the shard's slots (Database.SetKeywords, db.go:392-394): n must equal slot_count. */
+int pir_db_set_keywords(pir_db* db, const uint64_t* keywords, uint64_t n);
+uint32_t pir_db_slot_pitch(const pir_db* db);
+int pir_db_device(const pir_db* db);
+
+/* ---- the answer path -------------------------------------------------------------------------- */
+/*
+ * pir_answer: PrivateSecretSharedQuery (db.go:68-72).  out receives group_size*slot_bytes bytes:
+ * Shares[c].Data = out[c*slot_bytes .. (c+1)*slot_bytes).  For a shard handle the result is the
+ * shard's partial answer; XOR the partials of all shards (pir_xor_combine) for the server's answer.
+ */
+int pir_answer(pir_db* db, const pir_query* q, void* out, size_t out_len);
+/* n_queries independent queries answered in one pass over the database; out is n_queries
+ * consecutive answers of group_size*slot_bytes bytes (all queries must share group_size and
+ * is_keyword). */
+int pir_answer_batch(pir_db* db, const pir_query* qs, uint32_t n_queries, void* out, size_t out_len);
+/* ExpandSharedQuery (db.go:110-174): bits_out[r] in {0,1} for the shard's rows, one byte per row
+ * like Go's []bool.  n_rows must be the shard's row count for q->group_size. */
+int pir_expand_bits(pir_db* db, const pir_query* q, uint8_t* bits_out, uint64_t n_rows);
+/* PrivateSecretSharedQueryWithExpandedBits (db.go:75-107). */
+int pir_answer_with_bits(pir_db* db, uint32_t group_size, const uint8_t* bits, uint64_t n_rows,
+                         void* out, size_t out_len);
+/* Rows of the shard for a given group size: floor(db_size/W) restricted to the shard. */
+int pir_db_rows(const pir_db* db, uint32_t group_size, uint64_t* first_row, uint64_t* n_rows);
+
+/*
+ * Device-resident variants for callers that keep queries/answers in GPU memory and want to time
+ * the kernels alone: d_out is a device pointer (group_size*slot_bytes*n_queries bytes), stream is a
+ * cudaStream_t passed as void* (NULL = the handle's own stream).  The call only enqueues work.
+ */
+int pir_answer_batch_device(pir_db* db, const pir_query* qs, uint32_t n_queries, void* d_out,
+                            void* stream);
+
+/* ---- dpf package surface ---------------------------------------------------------------------- */
+/* (*Dpf).Evaluate2P (dpf/server.go:55-101) on n points: out[i] = Evaluate2P(share_number, key, xs[i])
+ * as wrapping int64.  Uses q->num_bits levels; runs on `device`. */
+int pir_dpf_eval_points(int device, const pir_query* q, const uint64_t* xs, uint64_t n, int64_t* out);
+
+/* ---- host helpers ----------------------------------------------------------------------------- */
+/* acc[i] ^= part[i]: XorSlots (slot.go:19-30) / Recover (query.go:278-297) / multi-GPU combine. */
+void pir_xor_combine(void* acc, const void* part, size_t len);
+/* numBits as the server computes it (db.go:114-121): floor(log2(rows))+1, or 32 for keyword queries. */
+uint32_t pir_num_bits_for(uint64_t db_size, uint32_t group_size, int is_keyword);
+
+/* counters for benchmarking: number of kernel launches issued by this library in this process */
+uint64_t pir_kernel_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PIR_B200_H */
