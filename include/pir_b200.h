@@ -134,6 +134,14 @@ int pir_answer_batch_device(pir_db* db, const pir_query* qs, uint32_t n_queries,
  * as wrapping int64.  Uses q->num_bits levels; runs on `device`. */
 int pir_dpf_eval_points(int device, const pir_query* q, const uint64_t* xs, uint64_t n, int64_t* out);
 
+/* ---- client side (host only; the "next" row N1 of SURVEY.md 8f) ------------------------------- */
+/* dpf.ClientInitialize + (*Dpf).GenerateTwoServer(a, b) (dpf/client.go:17-150): fills both servers'
+ * keys (prf keys, s_init, t_init, cw, final_cw, share_number, num_bits; group_size = 1, is_keyword = 0
+ * — the caller sets those two like newQueryShares does, query.go:83-98).  tape = the 97 bytes the
+ * reference would draw from crypto/rand in its order (4x16 PRF keys, 17, 16), or NULL for /dev/urandom. */
+int pir_client_gen_two_server(uint32_t num_bits, uint64_t a, uint64_t b, const uint8_t* tape,
+                              pir_query* q0, pir_query* q1);
+
 /* ---- host helpers ----------------------------------------------------------------------------- */
 /* acc[i] ^= part[i]: XorSlots (slot.go:19-30) / Recover (query.go:278-297) / multi-GPU combine. */
 void pir_xor_combine(void* acc, const void* part, size_t len);

@@ -1,0 +1,796 @@
+// capi.cu — the C ABI of include/pir_b200.h: handles, key marshalling, launch planning.
+// No CPU fallback exists: without a CUDA device every compute entry point returns PIR_ERR_CUDA.
+#include "../../include/pir_b200.h"
+#include "kernels.cuh"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <vector>
+
+using namespace pirb;
+
+// ---- errors -------------------------------------------------------------------------------------
+static thread_local char tl_err[512] = "";
+
+static int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(tl_err, sizeof tl_err, fmt, ap);
+    va_end(ap);
+    return code;
+}
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(e_ == cudaErrorMemoryAllocation ? PIR_ERR_OOM : PIR_ERR_CUDA, "%s: %s",    \
+                        #call, cudaGetErrorString(e_));                                            \
+    } while (0)
+
+extern "C" const char* pir_last_error(void) { return tl_err; }
+extern "C" int pir_abi_version(void) { return PIR_B200_ABI_VERSION; }
+extern "C" int pir_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+extern "C" uint64_t pir_kernel_launch_count(void) { return launch_count(); }
+
+// ---- host AES-128 key schedule (FIPS-197 5.2); the S-box is derived, not tabulated --------------
+namespace {
+struct AesHost {
+    uint8_t sbox[256];
+    uint32_t t0[256];
+    AesHost() {
+        auto mul = [](uint8_t a, uint8_t b) {
+            uint8_t p = 0;
+            while (b) {
+                if (b & 1) p ^= a;
+                a = (uint8_t)((a << 1) ^ ((a & 0x80) ? 0x1b : 0));
+                b >>= 1;
+            }
+            return p;
+        };
+        // walk the multiplicative group with generator 3: p = 3^k, q = 3^-k
+        uint8_t p = 1, q = 1;
+        do {
+            p = (uint8_t)(p ^ (p << 1) ^ ((p & 0x80) ? 0x1b : 0));  // p *= 3
+            q ^= (uint8_t)(q << 1);                                  // q /= 3
+            q ^= (uint8_t)(q << 2);
+            q ^= (uint8_t)(q << 4);
+            if (q & 0x80) q ^= 0x09;
+            uint8_t x = (uint8_t)(q ^ (uint8_t)((q << 1) | (q >> 7)) ^ (uint8_t)((q << 2) | (q >> 6)) ^
+                                  (uint8_t)((q << 3) | (q >> 5)) ^ (uint8_t)((q << 4) | (q >> 4)));
+            sbox[p] = (uint8_t)(x ^ 0x63);
+        } while (p != 1);
+        sbox[0] = 0x63;
+        for (int x = 0; x < 256; x++) {
+            uint8_t s = sbox[x];
+            t0[x] = (uint32_t)mul(s, 2) | ((uint32_t)s << 8) | ((uint32_t)s << 16) | ((uint32_t)mul(s, 3) << 24);
+        }
+    }
+    void expand(const uint8_t key[16], uint32_t rk[44]) const {
+        uint8_t w[176];
+        memcpy(w, key, 16);
+        uint8_t rc = 1;
+        for (int i = 16; i < 176; i += 4) {
+            uint8_t t[4] = {w[i - 4], w[i - 3], w[i - 2], w[i - 1]};
+            if ((i & 15) == 0) {
+                uint8_t t0_ = t[0];
+                t[0] = (uint8_t)(sbox[t[1]] ^ rc);
+                t[1] = sbox[t[2]];
+                t[2] = sbox[t[3]];
+                t[3] = sbox[t0_];
+                rc = (uint8_t)((rc << 1) ^ ((rc & 0x80) ? 0x1b : 0));
+            }
+            for (int j = 0; j < 4; j++) w[i + j] = (uint8_t)(w[i - 16 + j] ^ t[j]);
+        }
+        for (int i = 0; i < 44; i++)
+            rk[i] = (uint32_t)w[4 * i] | ((uint32_t)w[4 * i + 1] << 8) | ((uint32_t)w[4 * i + 2] << 16) |
+                    ((uint32_t)w[4 * i + 3] << 24);
+    }
+};
+const AesHost& aes_host() {
+    static AesHost a;
+    return a;
+}
+
+// ---- per-device context -------------------------------------------------------------------------
+struct DeviceCtx {
+    bool ready = false;
+    uint32_t* d_t0 = nullptr;
+    uint32_t smem_base = 0;
+    int num_sms = 0;
+};
+std::mutex g_dev_mu;
+DeviceCtx g_dev[64];
+
+int device_ctx(int device, DeviceCtx** out) {
+    int n = pir_device_count();
+    if (n <= 0) return fail(PIR_ERR_CUDA, "no CUDA device is visible (this library has no CPU path)");
+    if (device < 0 || device >= n || device >= 64) return fail(PIR_ERR_BAD_ARG, "device %d out of range (%d visible)", device, n);
+    std::lock_guard<std::mutex> lk(g_dev_mu);
+    DeviceCtx& c = g_dev[device];
+    if (!c.ready) {
+        CU(cudaSetDevice(device));
+        cudaDeviceProp prop;
+        CU(cudaGetDeviceProperties(&prop, device));
+        if (prop.major < 10)
+            return fail(PIR_ERR_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", device,
+                        prop.major, prop.minor);
+        c.num_sms = prop.multiProcessorCount;
+        CU(cudaMalloc(&c.d_t0, 1024));
+        CU(cudaMemcpy(c.d_t0, aes_host().t0, 1024, cudaMemcpyHostToDevice));
+        CU(configure_kernels());
+        CU(probe_smem_base(&c.smem_base));
+        if (c.smem_base >= 8192) return fail(PIR_ERR_CUDA, "unexpected dynamic shared memory base %u", c.smem_base);
+        c.ready = true;
+    }
+    *out = &c;
+    return PIR_OK;
+}
+
+uint32_t floor_log2_plus1(uint64_t h) {
+    uint32_t nb = 0;
+    while (h) {
+        nb++;
+        h >>= 1;
+    }
+    return nb;
+}
+}  // namespace
+
+extern "C" uint32_t pir_num_bits_for(uint64_t db_size, uint32_t group_size, int is_keyword) {
+    if (is_keyword) return 32;  // db.go:119-121
+    if (group_size == 0) return 0;
+    return floor_log2_plus1(db_size / group_size);  // db.go:114-117
+}
+
+extern "C" void pir_xor_combine(void* acc, const void* part, size_t len) {
+    uint8_t* a = (uint8_t*)acc;
+    const uint8_t* b = (const uint8_t*)part;
+    for (size_t i = 0; i < len; i++) a[i] ^= b[i];
+}
+
+// ---- query marshalling --------------------------------------------------------------------------
+static int build_query_const(const pir_query* q, uint32_t num_bits, QueryConst* qc) {
+    if (!q) return fail(PIR_ERR_BAD_ARG, "query is null");
+    if (!q->is_two_party) return fail(PIR_ERR_UNSUPPORTED, "multi-party keys are not supported (dpf/client.go:152-156)");
+    if (q->t_init > 1) return fail(PIR_ERR_BAD_KEY, "t_init must be 0 or 1");
+    if (q->share_number > 1) return fail(PIR_ERR_BAD_KEY, "share_number must be 0 or 1");
+    if (num_bits == 0 || num_bits > PIR_MAX_NUM_BITS) return fail(PIR_ERR_BAD_KEY, "num_bits %u out of range", num_bits);
+    memset(qc, 0, sizeof *qc);
+    for (int k = 0; k < 3; k++) aes_host().expand(q->prf_keys[k], qc->rk[k]);
+    for (uint32_t i = 0; i < num_bits; i++) {
+        const uint8_t* cw = q->cw[i];
+        for (int w = 0; w < 4; w++)
+            qc->cw[i][w] = (uint32_t)cw[4 * w] | ((uint32_t)cw[4 * w + 1] << 8) | ((uint32_t)cw[4 * w + 2] << 16) |
+                           ((uint32_t)cw[4 * w + 3] << 24);
+        qc->cw_tl |= (uint64_t)(cw[16] & 1) << i;
+        qc->cw_tr |= (uint64_t)(cw[17] & 1) << i;
+    }
+    for (int w = 0; w < 4; w++)
+        qc->s_init[w] = (uint32_t)q->s_init[4 * w] | ((uint32_t)q->s_init[4 * w + 1] << 8) |
+                        ((uint32_t)q->s_init[4 * w + 2] << 16) | ((uint32_t)q->s_init[4 * w + 3] << 24);
+    qc->t_init = q->t_init;
+    qc->fcw_parity = (uint32_t)((uint64_t)q->final_cw & 1u);
+    qc->num_bits = num_bits;
+    qc->share_number = q->share_number;
+    qc->final_cw = q->final_cw;
+    return PIR_OK;
+}
+
+// ---- database handle ----------------------------------------------------------------------------
+struct pir_db {
+    int device = 0;
+    DeviceCtx* ctx = nullptr;
+    uint64_t db_size = 0;
+    uint32_t slot_bytes = 0;
+    uint32_t pitch = 0;
+    uint64_t slot_begin = 0, slot_count = 0;
+    uint8_t* d_slots = nullptr;
+    uint64_t* d_keywords = nullptr;
+    cudaStream_t stream = nullptr;
+    std::mutex mu;
+    // grow-only scratch
+    uint4* d_front_s[2] = {nullptr, nullptr};
+    uint8_t* d_front_t[2] = {nullptr, nullptr};
+    uint64_t front_cap = 0;
+    uint8_t* d_bits = nullptr;
+    uint64_t bits_cap = 0;
+    uint8_t* d_out = nullptr;
+    uint64_t out_cap = 0;
+    uint8_t* h_out = nullptr;  // pinned
+    uint64_t h_out_cap = 0;
+};
+
+namespace {
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev);
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+int ensure_front(pir_db* db, uint64_t n) {
+    if (n <= db->front_cap) return PIR_OK;
+    for (int k = 0; k < 2; k++) {
+        if (db->d_front_s[k]) cudaFree(db->d_front_s[k]);
+        if (db->d_front_t[k]) cudaFree(db->d_front_t[k]);
+        db->d_front_s[k] = nullptr;
+        db->d_front_t[k] = nullptr;
+    }
+    db->front_cap = 0;
+    for (int k = 0; k < 2; k++) {
+        CU(cudaMalloc(&db->d_front_s[k], n * sizeof(uint4)));
+        CU(cudaMalloc(&db->d_front_t[k], n));
+    }
+    db->front_cap = n;
+    return PIR_OK;
+}
+int ensure_bits(pir_db* db, uint64_t n) {
+    if (n <= db->bits_cap) return PIR_OK;
+    if (db->d_bits) cudaFree(db->d_bits);
+    db->d_bits = nullptr;
+    db->bits_cap = 0;
+    CU(cudaMalloc(&db->d_bits, n));
+    db->bits_cap = n;
+    return PIR_OK;
+}
+int ensure_out(pir_db* db, uint64_t n) {
+    if (n > db->out_cap) {
+        if (db->d_out) cudaFree(db->d_out);
+        db->d_out = nullptr;
+        db->out_cap = 0;
+        CU(cudaMalloc(&db->d_out, n));
+        db->out_cap = n;
+    }
+    if (n > db->h_out_cap) {
+        if (db->h_out) cudaFreeHost(db->h_out);
+        db->h_out = nullptr;
+        db->h_out_cap = 0;
+        CU(cudaMallocHost(&db->h_out, n));
+        db->h_out_cap = n;
+    }
+    return PIR_OK;
+}
+
+// rows of the shard for group size W (global row indices)
+int shard_rows(const pir_db* db, uint32_t W, uint64_t* first_row, uint64_t* n_rows) {
+    if (W == 0) return fail(PIR_ERR_BAD_ARG, "group_size must be >= 1");
+    uint64_t H = db->db_size / W;  // db.go:79,114: integer division
+    if (db->slot_begin % W) return fail(PIR_ERR_BAD_ARG, "shard start %llu is not a multiple of group_size %u",
+                                        (unsigned long long)db->slot_begin, W);
+    uint64_t r0 = db->slot_begin / W;
+    uint64_t end_slot = db->slot_begin + db->slot_count;
+    if (end_slot != db->db_size && (db->slot_count % W))
+        return fail(PIR_ERR_BAD_ARG, "shard length %llu is not a multiple of group_size %u",
+                    (unsigned long long)db->slot_count, W);
+    uint64_t r1 = end_slot / W;
+    if (r1 > H) r1 = H;
+    if (r0 > r1) r0 = r1;
+    *first_row = r0;
+    *n_rows = r1 - r0;
+    return PIR_OK;
+}
+
+struct Plan {
+    uint32_t D, B, Fc;
+    uint64_t task_first, task_count;
+};
+
+// Choose the per-thread depth D and CTA breadth B (kernels.cuh) for a shard of rows.
+Plan make_plan(uint32_t nb, uint64_t first_row, uint64_t n_rows, int num_sms) {
+    Plan best{};
+    double best_score = -1.0;
+    uint32_t Bmax = nb - 1 < (uint32_t)kFusedLogThreads ? nb - 1 : (uint32_t)kFusedLogThreads;
+    int forced = -1;
+    if (const char* e = getenv("PIRB_DFS_DEPTH")) forced = atoi(e);
+    for (int D = kMaxDfsDepth; D >= 0; D--) {
+        if ((uint32_t)D + Bmax > nb - 1) continue;
+        if (forced >= 0 && D != forced && (uint32_t)forced + Bmax <= nb - 1) continue;
+        uint32_t B = Bmax;
+        uint32_t Fc = nb - 1 - (uint32_t)D - B;
+        uint32_t sh = nb - Fc;  // rows per task = 2^sh
+        uint64_t t0 = first_row >> sh, t1 = (first_row + n_rows - 1) >> sh;
+        uint64_t tasks = t1 - t0 + 1;
+        uint64_t waves = (tasks + num_sms - 1) / num_sms;
+        double balance = (double)tasks / (double)(waves * num_sms);
+        double dfs = 16.0 * ((double)(2u << D) - 1.0);
+        double score = balance * dfs / (dfs + 28.0);
+        if (score > best_score) {
+            best_score = score;
+            best = Plan{(uint32_t)D, B, Fc, t0, tasks};
+        }
+    }
+    return best;
+}
+}  // namespace
+
+extern "C" int pir_db_create(int device, uint64_t db_size, uint32_t slot_bytes, uint64_t slot_begin,
+                             uint64_t slot_count, pir_db** out) {
+    if (!out) return fail(PIR_ERR_BAD_ARG, "out is null");
+    *out = nullptr;
+    if (db_size == 0 || slot_bytes == 0) return fail(PIR_ERR_BAD_ARG, "db_size and slot_bytes must be non-zero");
+    if (slot_begin > db_size || slot_count > db_size - slot_begin)
+        return fail(PIR_ERR_BAD_ARG, "shard [%llu, +%llu) exceeds db_size %llu", (unsigned long long)slot_begin,
+                    (unsigned long long)slot_count, (unsigned long long)db_size);
+    DeviceCtx* ctx = nullptr;
+    int rc = device_ctx(device, &ctx);
+    if (rc) return rc;
+    DeviceGuard g(device);
+    pir_db* db = new (std::nothrow) pir_db();
+    if (!db) return fail(PIR_ERR_OOM, "host allocation failed");
+    db->device = device;
+    db->ctx = ctx;
+    db->db_size = db_size;
+    db->slot_bytes = slot_bytes;
+    db->pitch = (slot_bytes + 15u) & ~15u;
+    db->slot_begin = slot_begin;
+    db->slot_count = slot_count;
+    uint64_t bytes = slot_count * (uint64_t)db->pitch;
+    cudaError_t e = cudaStreamCreateWithFlags(&db->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMalloc(&db->d_slots, bytes ? bytes : 16);
+    if (e == cudaSuccess && db->pitch != slot_bytes) e = cudaMemset(db->d_slots, 0, bytes ? bytes : 16);
+    if (e != cudaSuccess) {
+        int code = e == cudaErrorMemoryAllocation ? PIR_ERR_OOM : PIR_ERR_CUDA;
+        fail(code, "pir_db_create: %s", cudaGetErrorString(e));
+        cudaGetLastError();
+        pir_db_destroy(db);
+        return code;
+    }
+    *out = db;
+    return PIR_OK;
+}
+
+extern "C" int pir_db_destroy(pir_db* db) {
+    if (!db) return PIR_OK;
+    DeviceGuard g(db->device);
+    if (db->stream) cudaStreamSynchronize(db->stream);
+    for (int k = 0; k < 2; k++) {
+        if (db->d_front_s[k]) cudaFree(db->d_front_s[k]);
+        if (db->d_front_t[k]) cudaFree(db->d_front_t[k]);
+    }
+    if (db->d_bits) cudaFree(db->d_bits);
+    if (db->d_out) cudaFree(db->d_out);
+    if (db->h_out) cudaFreeHost(db->h_out);
+    if (db->d_keywords) cudaFree(db->d_keywords);
+    if (db->d_slots) cudaFree(db->d_slots);
+    if (db->stream) cudaStreamDestroy(db->stream);
+    delete db;
+    return PIR_OK;
+}
+
+extern "C" uint32_t pir_db_slot_pitch(const pir_db* db) { return db ? db->pitch : 0; }
+extern "C" int pir_db_device(const pir_db* db) { return db ? db->device : -1; }
+
+static int check_slot_range(const pir_db* db, uint64_t slot_index, uint64_t n_slots) {
+    if (slot_index < db->slot_begin || slot_index - db->slot_begin > db->slot_count ||
+        n_slots > db->slot_count - (slot_index - db->slot_begin))
+        return fail(PIR_ERR_BAD_ARG, "slots [%llu, +%llu) are outside the shard", (unsigned long long)slot_index,
+                    (unsigned long long)n_slots);
+    return PIR_OK;
+}
+
+extern "C" int pir_db_upload(pir_db* db, uint64_t slot_index, const void* host_slots, uint64_t n_slots) {
+    if (!db || (!host_slots && n_slots)) return fail(PIR_ERR_BAD_ARG, "null argument");
+    int rc = check_slot_range(db, slot_index, n_slots);
+    if (rc || n_slots == 0) return rc;
+    std::lock_guard<std::mutex> lk(db->mu);
+    DeviceGuard g(db->device);
+    uint8_t* dst = db->d_slots + (slot_index - db->slot_begin) * (uint64_t)db->pitch;
+    CU(cudaStreamSynchronize(db->stream));
+    if (db->pitch == db->slot_bytes)
+        CU(cudaMemcpy(dst, host_slots, n_slots * (uint64_t)db->slot_bytes, cudaMemcpyHostToDevice));
+    else
+        CU(cudaMemcpy2D(dst, db->pitch, host_slots, db->slot_bytes, db->slot_bytes, n_slots, cudaMemcpyHostToDevice));
+    return PIR_OK;
+}
+
+extern "C" int pir_db_download(pir_db* db, uint64_t slot_index, void* host_slots, uint64_t n_slots) {
+    if (!db || (!host_slots && n_slots)) return fail(PIR_ERR_BAD_ARG, "null argument");
+    int rc = check_slot_range(db, slot_index, n_slots);
+    if (rc || n_slots == 0) return rc;
+    std::lock_guard<std::mutex> lk(db->mu);
+    DeviceGuard g(db->device);
+    const uint8_t* src = db->d_slots + (slot_index - db->slot_begin) * (uint64_t)db->pitch;
+    CU(cudaStreamSynchronize(db->stream));
+    if (db->pitch == db->slot_bytes)
+        CU(cudaMemcpy(host_slots, src, n_slots * (uint64_t)db->slot_bytes, cudaMemcpyDeviceToHost));
+    else
+        CU(cudaMemcpy2D(host_slots, db->slot_bytes, src, db->pitch, db->slot_bytes, n_slots, cudaMemcpyDeviceToHost));
+    return PIR_OK;
+}
+
+extern "C" int pir_db_fill_synthetic(pir_db* db, uint64_t seed) {
+    if (!db) return fail(PIR_ERR_BAD_ARG, "null handle");
+    std::lock_guard<std::mutex> lk(db->mu);
+    DeviceGuard g(db->device);
+    CU(launch_synth_fill(db->d_slots, db->slot_begin, db->slot_count, db->slot_bytes, db->pitch, seed, db->stream));
+    CU(cudaStreamSynchronize(db->stream));
+    return PIR_OK;
+}
+
+extern "C" int pir_db_set_keywords(pir_db* db, const uint64_t* keywords, uint64_t n) {
+    if (!db || !keywords) return fail(PIR_ERR_BAD_ARG, "null argument");
+    if (n != db->slot_count) return fail(PIR_ERR_BAD_ARG, "expected %llu keywords (one per shard slot), got %llu",
+                                         (unsigned long long)db->slot_count, (unsigned long long)n);
+    std::lock_guard<std::mutex> lk(db->mu);
+    DeviceGuard g(db->device);
+    if (!db->d_keywords) CU(cudaMalloc(&db->d_keywords, (n ? n : 1) * sizeof(uint64_t)));
+    CU(cudaStreamSynchronize(db->stream));
+    CU(cudaMemcpy(db->d_keywords, keywords, n * sizeof(uint64_t), cudaMemcpyHostToDevice));
+    return PIR_OK;
+}
+
+extern "C" int pir_db_rows(const pir_db* db, uint32_t group_size, uint64_t* first_row, uint64_t* n_rows) {
+    if (!db || !first_row || !n_rows) return fail(PIR_ERR_BAD_ARG, "null argument");
+    return shard_rows(db, group_size, first_row, n_rows);
+}
+
+// ---- the answer path ----------------------------------------------------------------------------
+namespace {
+struct QueryGeom {
+    uint32_t W;
+    uint32_t nb;
+    uint64_t first_row, n_rows;
+    uint64_t row_bytes;  // pitched
+};
+
+int query_geom(const pir_db* db, const pir_query* q, QueryGeom* g) {
+    if (!q) return fail(PIR_ERR_BAD_ARG, "query is null");
+    if (q->reserved != 0) return fail(PIR_ERR_BAD_ARG, "pir_query.reserved must be 0");
+    g->W = q->group_size;
+    int rc = shard_rows(db, g->W, &g->first_row, &g->n_rows);
+    if (rc) return rc;
+    g->nb = pir_num_bits_for(db->db_size, g->W, q->is_keyword);
+    if (q->num_bits != 0 && g->nb != 0 && q->num_bits != g->nb)
+        return fail(PIR_ERR_BAD_KEY, "key has %u correction words but this database needs %u (db.go:114-121)",
+                    q->num_bits, g->nb);
+    g->row_bytes = (uint64_t)g->W * db->pitch;
+    return PIR_OK;
+}
+
+// Enqueue one query's work on `st`; d_out receives the pitched answer (row_bytes bytes).
+int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* d_out, cudaStream_t st) {
+    CU(cudaMemsetAsync(d_out, 0, g.row_bytes, st));
+    if (g.n_rows == 0) return PIR_OK;
+    QueryConst qc;
+    int rc = build_query_const(q, g.nb, &qc);
+    if (rc) return rc;
+    const DeviceCtx& ctx = *db->ctx;
+    if (q->is_keyword) {
+        if (!db->d_keywords) return fail(PIR_ERR_BAD_ARG, "keyword query on a database without keywords (pir_db_set_keywords)");
+        if (g.first_row < db->slot_begin || g.first_row + g.n_rows > db->slot_begin + db->slot_count)
+            return fail(PIR_ERR_BAD_ARG, "keyword queries with group_size > 1 need an unsharded handle");
+        if ((rc = ensure_bits(db, g.n_rows))) return rc;
+        CU(launch_eval_points(qc, db->d_keywords + (g.first_row - db->slot_begin), 0, g.n_rows, nullptr,
+                              db->d_bits, ctx.d_t0, ctx.smem_base, st));
+        CU(launch_scan_bytes(db->d_slots, g.row_bytes, g.n_rows, db->d_bits, (uint32_t*)d_out, ctx.num_sms, st));
+        return PIR_OK;
+    }
+    Plan p = make_plan(g.nb, g.first_row, g.n_rows, ctx.num_sms);
+    if ((rc = ensure_front(db, p.task_count + 2))) return rc;
+    TopPlan tp{};
+    tp.Fc = p.Fc;
+    tp.task_first = p.task_first;
+    tp.task_count = p.task_count;
+    for (int k = 0; k < 2; k++) {
+        tp.buf_s[k] = db->d_front_s[k];
+        tp.buf_t[k] = db->d_front_t[k];
+    }
+    CU(launch_top(qc, tp, ctx.d_t0, ctx.smem_base, st));
+    FusedPlan fp{};
+    fp.db = db->d_slots;
+    fp.row_bytes = g.row_bytes;
+    fp.first_row = g.first_row;
+    fp.n_rows = g.n_rows;
+    fp.D = p.D;
+    fp.B = p.B;
+    fp.Fc = p.Fc;
+    fp.task_first = p.task_first;
+    fp.task_count = p.task_count;
+    fp.frontier_s = db->d_front_s[p.Fc & 1];
+    fp.frontier_t = db->d_front_t[p.Fc & 1];
+    fp.out = (uint32_t*)d_out;
+    const bool fused = fused_supports_row_bytes(g.row_bytes) && !getenv("PIRB_FORCE_UNFUSED");
+    if (fused) {
+        CU(launch_fused(qc, fp, false, ctx.d_t0, ctx.smem_base, ctx.num_sms, st));
+    } else {
+        if ((rc = ensure_bits(db, g.n_rows))) return rc;
+        fp.bits_out = db->d_bits;
+        fp.row_bytes = 16;  // unused in BITS mode; keeps the kernel's row geometry trivial
+        CU(launch_fused(qc, fp, true, ctx.d_t0, ctx.smem_base, ctx.num_sms, st));
+        CU(launch_scan_bytes(db->d_slots, g.row_bytes, g.n_rows, db->d_bits, (uint32_t*)d_out, ctx.num_sms, st));
+    }
+    return PIR_OK;
+}
+
+// pitched device answer -> dense host answer (Shares[c].Data = out[c*S, (c+1)*S))
+void compact_answer(const pir_db* db, uint32_t W, const uint8_t* pitched, uint8_t* dense) {
+    for (uint32_t c = 0; c < W; c++) memcpy(dense + (size_t)c * db->slot_bytes, pitched + (size_t)c * db->pitch, db->slot_bytes);
+}
+}  // namespace
+
+extern "C" int pir_answer_batch_device(pir_db* db, const pir_query* qs, uint32_t n_queries, void* d_out,
+                                       void* stream) {
+    if (!db || !qs || !d_out || n_queries == 0) return fail(PIR_ERR_BAD_ARG, "null or empty argument");
+    std::lock_guard<std::mutex> lk(db->mu);
+    DeviceGuard g(db->device);
+    cudaStream_t st = stream ? (cudaStream_t)stream : db->stream;
+    for (uint32_t i = 0; i < n_queries; i++) {
+        QueryGeom geom;
+        int rc = query_geom(db, &qs[i], &geom);
+        if (rc) return rc;
+        if (qs[i].group_size != qs[0].group_size || qs[i].is_keyword != qs[0].is_keyword)
+            return fail(PIR_ERR_BAD_ARG, "all queries of a batch must share group_size and is_keyword");
+        rc = enqueue_answer(db, &qs[i], geom, (uint8_t*)d_out + (uint64_t)i * geom.row_bytes, st);
+        if (rc) return rc;
+    }
+    return PIR_OK;
+}
+
+extern "C" int pir_answer_batch(pir_db* db, const pir_query* qs, uint32_t n_queries, void* out, size_t out_len) {
+    if (!db || !qs || !out || n_queries == 0) return fail(PIR_ERR_BAD_ARG, "null or empty argument");
+    std::lock_guard<std::mutex> lk(db->mu);
+    DeviceGuard g(db->device);
+    QueryGeom g0;
+    int rc = query_geom(db, &qs[0], &g0);
+    if (rc) return rc;
+    const size_t ans = (size_t)g0.W * db->slot_bytes;
+    if (out_len < ans * n_queries) return fail(PIR_ERR_BAD_ARG, "out_len %zu < %zu", out_len, ans * n_queries);
+    if ((rc = ensure_out(db, g0.row_bytes * n_queries))) return rc;
+    for (uint32_t i = 0; i < n_queries; i++) {
+        QueryGeom geom;
+        if ((rc = query_geom(db, &qs[i], &geom))) return rc;
+        if (qs[i].group_size != qs[0].group_size || qs[i].is_keyword != qs[0].is_keyword)
+            return fail(PIR_ERR_BAD_ARG, "all queries of a batch must share group_size and is_keyword");
+        if ((rc = enqueue_answer(db, &qs[i], geom, db->d_out + (uint64_t)i * geom.row_bytes, db->stream))) {
+            cudaStreamSynchronize(db->stream);
+            return rc;
+        }
+    }
+    CU(cudaMemcpyAsync(db->h_out, db->d_out, g0.row_bytes * n_queries, cudaMemcpyDeviceToHost, db->stream));
+    CU(cudaStreamSynchronize(db->stream));
+    for (uint32_t i = 0; i < n_queries; i++)
+        compact_answer(db, g0.W, db->h_out + (uint64_t)i * g0.row_bytes, (uint8_t*)out + (size_t)i * ans);
+    return PIR_OK;
+}
+
+extern "C" int pir_answer(pir_db* db, const pir_query* q, void* out, size_t out_len) {
+    return pir_answer_batch(db, q, 1, out, out_len);
+}
+
+extern "C" int pir_expand_bits(pir_db* db, const pir_query* q, uint8_t* bits_out, uint64_t n_rows) {
+    if (!db || !q || (!bits_out && n_rows)) return fail(PIR_ERR_BAD_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(db->mu);
+    DeviceGuard g(db->device);
+    QueryGeom geom;
+    int rc = query_geom(db, q, &geom);
+    if (rc) return rc;
+    if (n_rows != geom.n_rows) return fail(PIR_ERR_BAD_ARG, "n_rows %llu != shard rows %llu",
+                                           (unsigned long long)n_rows, (unsigned long long)geom.n_rows);
+    if (n_rows == 0) return PIR_OK;
+    QueryConst qc;
+    if ((rc = build_query_const(q, geom.nb, &qc))) return rc;
+    if ((rc = ensure_bits(db, n_rows))) return rc;
+    const DeviceCtx& ctx = *db->ctx;
+    if (q->is_keyword) {
+        if (!db->d_keywords) return fail(PIR_ERR_BAD_ARG, "keyword query on a database without keywords");
+        if (geom.first_row < db->slot_begin || geom.first_row + geom.n_rows > db->slot_begin + db->slot_count)
+            return fail(PIR_ERR_BAD_ARG, "keyword queries with group_size > 1 need an unsharded handle");
+        CU(launch_eval_points(qc, db->d_keywords + (geom.first_row - db->slot_begin), 0, n_rows, nullptr,
+                              db->d_bits, ctx.d_t0, ctx.smem_base, db->stream));
+    } else {
+        Plan p = make_plan(geom.nb, geom.first_row, geom.n_rows, ctx.num_sms);
+        if ((rc = ensure_front(db, p.task_count + 2))) return rc;
+        TopPlan tp{};
+        tp.Fc = p.Fc;
+        tp.task_first = p.task_first;
+        tp.task_count = p.task_count;
+        for (int k = 0; k < 2; k++) {
+            tp.buf_s[k] = db->d_front_s[k];
+            tp.buf_t[k] = db->d_front_t[k];
+        }
+        CU(launch_top(qc, tp, ctx.d_t0, ctx.smem_base, db->stream));
+        FusedPlan fp{};
+        fp.db = db->d_slots;
+        fp.row_bytes = 16;
+        fp.first_row = geom.first_row;
+        fp.n_rows = geom.n_rows;
+        fp.D = p.D;
+        fp.B = p.B;
+        fp.Fc = p.Fc;
+        fp.task_first = p.task_first;
+        fp.task_count = p.task_count;
+        fp.frontier_s = db->d_front_s[p.Fc & 1];
+        fp.frontier_t = db->d_front_t[p.Fc & 1];
+        fp.bits_out = db->d_bits;
+        CU(launch_fused(qc, fp, true, ctx.d_t0, ctx.smem_base, ctx.num_sms, db->stream));
+    }
+    CU(cudaMemcpyAsync(bits_out, db->d_bits, n_rows, cudaMemcpyDeviceToHost, db->stream));
+    CU(cudaStreamSynchronize(db->stream));
+    return PIR_OK;
+}
+
+extern "C" int pir_answer_with_bits(pir_db* db, uint32_t group_size, const uint8_t* bits, uint64_t n_rows,
+                                    void* out, size_t out_len) {
+    if (!db || (!bits && n_rows) || !out) return fail(PIR_ERR_BAD_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(db->mu);
+    DeviceGuard g(db->device);
+    uint64_t first_row, rows;
+    int rc = shard_rows(db, group_size, &first_row, &rows);
+    if (rc) return rc;
+    if (n_rows != rows) return fail(PIR_ERR_BAD_ARG, "n_rows %llu != shard rows %llu", (unsigned long long)n_rows,
+                                    (unsigned long long)rows);
+    const size_t ans = (size_t)group_size * db->slot_bytes;
+    if (out_len < ans) return fail(PIR_ERR_BAD_ARG, "out_len %zu < %zu", out_len, ans);
+    const uint64_t row_bytes = (uint64_t)group_size * db->pitch;
+    if ((rc = ensure_out(db, row_bytes))) return rc;
+    if ((rc = ensure_bits(db, n_rows ? n_rows : 1))) return rc;
+    CU(cudaMemsetAsync(db->d_out, 0, row_bytes, db->stream));
+    if (n_rows) {
+        CU(cudaMemcpyAsync(db->d_bits, bits, n_rows, cudaMemcpyHostToDevice, db->stream));
+        CU(launch_scan_bytes(db->d_slots, row_bytes, n_rows, db->d_bits, (uint32_t*)db->d_out, db->ctx->num_sms,
+                             db->stream));
+    }
+    CU(cudaMemcpyAsync(db->h_out, db->d_out, row_bytes, cudaMemcpyDeviceToHost, db->stream));
+    CU(cudaStreamSynchronize(db->stream));
+    compact_answer(db, group_size, db->h_out, (uint8_t*)out);
+    return PIR_OK;
+}
+
+extern "C" int pir_dpf_eval_points(int device, const pir_query* q, const uint64_t* xs, uint64_t n, int64_t* out) {
+    if (!q || (!xs && n) || (!out && n)) return fail(PIR_ERR_BAD_ARG, "null argument");
+    DeviceCtx* ctx = nullptr;
+    int rc = device_ctx(device, &ctx);
+    if (rc) return rc;
+    QueryConst qc;
+    if ((rc = build_query_const(q, q->num_bits, &qc))) return rc;
+    if (n == 0) return PIR_OK;
+    DeviceGuard g(device);
+    uint64_t* d_x = nullptr;
+    int64_t* d_v = nullptr;
+    CU(cudaMalloc(&d_x, n * 8));
+    cudaError_t e = cudaMalloc(&d_v, n * 8);
+    if (e == cudaSuccess) e = cudaMemcpy(d_x, xs, n * 8, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = launch_eval_points(qc, d_x, 0, n, d_v, nullptr, ctx->d_t0, ctx->smem_base, 0);
+    if (e == cudaSuccess) e = cudaMemcpy(out, d_v, n * 8, cudaMemcpyDeviceToHost);
+    cudaFree(d_x);
+    if (d_v) cudaFree(d_v);
+    if (e != cudaSuccess) return fail(PIR_ERR_CUDA, "pir_dpf_eval_points: %s", cudaGetErrorString(e));
+    return PIR_OK;
+}
+
+// ---- client side (row N1 of the scope table): key generation on the host ------------------------
+namespace {
+// AES-128 encryption of one block on the host, straight from FIPS-197 (byte oriented).
+void aes_encrypt_host(const uint32_t rk[44], const uint8_t in[16], uint8_t out[16]) {
+    const AesHost& A = aes_host();
+    uint8_t st[16], tmp[16];
+    auto add_key = [&](int round) {
+        for (int c = 0; c < 4; c++) {
+            uint32_t w = rk[4 * round + c];
+            for (int r = 0; r < 4; r++) st[4 * c + r] ^= (uint8_t)(w >> (8 * r));
+        }
+    };
+    auto xt = [](uint8_t v) { return (uint8_t)((v << 1) ^ ((v & 0x80) ? 0x1b : 0)); };
+    memcpy(st, in, 16);
+    add_key(0);
+    for (int round = 1; round <= 10; round++) {
+        for (int c = 0; c < 4; c++)
+            for (int r = 0; r < 4; r++) tmp[4 * c + r] = A.sbox[st[4 * ((c + r) & 3) + r]];
+        if (round < 10) {
+            for (int c = 0; c < 4; c++) {
+                const uint8_t* a = tmp + 4 * c;
+                uint8_t all = (uint8_t)(a[0] ^ a[1] ^ a[2] ^ a[3]);
+                for (int r = 0; r < 4; r++) st[4 * c + r] = (uint8_t)(a[r] ^ all ^ xt((uint8_t)(a[r] ^ a[(r + 1) & 3])));
+            }
+        } else {
+            memcpy(st, tmp, 16);
+        }
+        add_key(round);
+    }
+    memcpy(out, st, 16);
+}
+
+// prf(x, FixedBlocks, 3, ...) of dpf/common.go:62-75
+void prf3_host(const uint32_t rk[3][44], const uint8_t x[16], uint8_t out[48]) {
+    for (int k = 0; k < 3; k++) {
+        aes_encrypt_host(rk[k], x, out + 16 * k);
+        for (int j = 0; j < 16; j++) out[16 * k + j] ^= x[j];
+    }
+}
+
+// binary.Varint(buf[:8]) as used at dpf/client.go:141-142
+int64_t varint8_host(const uint8_t* s) {
+    uint64_t acc = 0;
+    for (int j = 0; j < 8; j++) {
+        if (s[j] < 0x80) {
+            uint64_t ux = acc | ((uint64_t)s[j] << (7 * j));
+            uint64_t v = ux >> 1;
+            return (int64_t)((ux & 1) ? ~v : v);
+        }
+        acc |= (uint64_t)(s[j] & 0x7f) << (7 * j);
+    }
+    return 0;
+}
+}  // namespace
+
+// dpf.ClientInitialize + (*Dpf).GenerateTwoServer (dpf/client.go:17-150).  `tape` supplies the 97
+// bytes the reference draws from crypto/rand, in its order (4x16 PRF keys, 17, 16); NULL = /dev/urandom.
+extern "C" int pir_client_gen_two_server(uint32_t num_bits, uint64_t a, uint64_t b, const uint8_t* tape,
+                                         pir_query* q0, pir_query* q1) {
+    if (!q0 || !q1) return fail(PIR_ERR_BAD_ARG, "null key output");
+    if (num_bits == 0 || num_bits > PIR_MAX_NUM_BITS) return fail(PIR_ERR_BAD_KEY, "num_bits %u out of range", num_bits);
+    uint8_t rnd[97];
+    if (tape) {
+        memcpy(rnd, tape, 97);
+    } else {
+        FILE* f = fopen("/dev/urandom", "rb");
+        if (!f || fread(rnd, 1, 97, f) != 97) {
+            if (f) fclose(f);
+            return fail(PIR_ERR_BAD_ARG, "cannot read /dev/urandom");
+        }
+        fclose(f);
+    }
+    pir_query* qs[2] = {q0, q1};
+    for (int p = 0; p < 2; p++) {
+        memset(qs[p], 0, sizeof(pir_query));
+        memcpy(qs[p]->prf_keys, rnd, 64);
+        qs[p]->share_number = (uint8_t)p;
+        qs[p]->is_two_party = 1;
+        qs[p]->num_bits = num_bits;
+        qs[p]->group_size = 1;
+    }
+    uint32_t rk[3][44];
+    for (int k = 0; k < 3; k++) aes_host().expand(rnd + 16 * k, rk[k]);
+    memcpy(q0->s_init, rnd + 64, 16);
+    q0->t_init = rnd[80] & 1;
+    memcpy(q1->s_init, rnd + 81, 16);
+    q1->t_init = q0->t_init ^ 1;
+    uint8_t s[2][16], t[2] = {q0->t_init, q1->t_init};
+    memcpy(s[0], q0->s_init, 16);
+    memcpy(s[1], q1->s_init, 16);
+    for (uint32_t i = 0; i < num_bits; i++) {
+        uint8_t g[2][48];
+        prf3_host(rk, s[0], g[0]);
+        prf3_host(rk, s[1], g[1]);
+        const uint8_t abit = (uint8_t)((a >> (num_bits - 1 - i)) & 1);
+        const int keep = abit ? 17 : 0, lose = abit ? 0 : 17;
+        uint8_t* cw = q0->cw[i];
+        for (int j = 0; j < 16; j++) cw[j] = g[0][lose + j] ^ g[1][lose + j];
+        cw[16] = (uint8_t)((g[0][16] & 1) ^ (g[1][16] & 1) ^ abit ^ 1);
+        cw[17] = (uint8_t)((g[0][33] & 1) ^ (g[1][33] & 1) ^ abit);
+        const uint8_t tkeep = abit ? cw[17] : cw[16];
+        for (int p = 0; p < 2; p++) {
+            for (int j = 0; j < 16; j++) s[p][j] = (uint8_t)(g[p][keep + j] ^ (t[p] ? cw[j] : 0));
+            t[p] = (uint8_t)((g[p][keep + 16] & 1) ^ (tkeep & t[p]));
+        }
+        memcpy(q1->cw[i], cw, PIR_CW_BYTES);
+    }
+    uint64_t f = b - (uint64_t)varint8_host(s[0]) + (uint64_t)varint8_host(s[1]);
+    if (t[1] == 1) f = 0 - f;
+    q0->final_cw = q1->final_cw = (int64_t)f;
+    return PIR_OK;
+}
+
+// ---- debugging hooks for the CPU test-suite (host logic only, no device needed) -----------------
+extern "C" void pir_debug_round_keys(const uint8_t key[16], uint32_t rk[44]) { aes_host().expand(key, rk); }
+extern "C" void pir_debug_t0(uint32_t t0[256]) { memcpy(t0, aes_host().t0, 1024); }
+extern "C" void pir_debug_plan(uint32_t nb, uint64_t first_row, uint64_t n_rows, int num_sms, uint32_t* D,
+                               uint32_t* B, uint32_t* Fc, uint64_t* task_first, uint64_t* task_count) {
+    Plan p = make_plan(nb, first_row, n_rows, num_sms);
+    *D = p.D; *B = p.B; *Fc = p.Fc; *task_first = p.task_first; *task_count = p.task_count;
+}

@@ -1,0 +1,67 @@
+// kernels.cuh — launch-side declarations shared by kernels.cu (device code) and capi.cu (C ABI).
+#pragma once
+#include <stdint.h>
+#include <cuda_runtime.h>
+#include "dpf_device.cuh"
+
+namespace pirb {
+
+constexpr int kFusedThreads = 512;  // threads per CTA of the fused kernel (one CTA per SM)
+constexpr int kFusedLogThreads = 9;
+constexpr int kMaxDfsDepth = 7;     // per-thread DFS depth D: a thread owns 2^(D+1) rows
+constexpr int kTopThreads = 1024;
+
+// Geometry of one fused launch over a shard (all row numbers are GLOBAL row indices of the DPF
+// domain; the shard's first row is stored at `db`).
+struct FusedPlan {
+    const uint8_t* db;        // shard base (row `first_row` lives here)
+    uint64_t row_bytes;       // W * slot_pitch, multiple of 16
+    uint64_t first_row;       // first global row of the shard
+    uint64_t n_rows;          // rows in the shard
+    uint32_t D;               // per-thread DFS depth
+    uint32_t B;               // CTA-level BFS levels: 2^B threads get a subtree each
+    uint32_t Fc;              // tree level of the CTA tasks = num_bits-1-D-B
+    uint32_t pad;
+    uint64_t task_first;      // first CTA task (node index at level Fc) touching the shard
+    uint64_t task_count;
+    const uint4* frontier_s;  // task_count seeds at level Fc (from the top kernel)
+    const uint8_t* frontier_t;
+    uint32_t* out;            // SCAN mode: row_bytes/4 words, zeroed before launch (atomic XOR)
+    uint8_t* bits_out;        // BITS mode: one byte per shard row
+};
+
+struct TopPlan {
+    uint32_t Fc;          // produce nodes of level Fc
+    uint32_t pad;
+    uint64_t task_first;  // node index range wanted at level Fc
+    uint64_t task_count;
+    uint4* buf_s[2];      // ping-pong level buffers, each >= task_count + 2 entries
+    uint8_t* buf_t[2];
+    // the result is left in buf_s[Fc & 1], entry j = node task_first + j
+};
+
+// row layout kinds handled by the fused kernel: chunks of 16 B per row
+//   c = 1,2,4,8,16,32  -> one accumulator per lane
+//   c = 64,128,256     -> c/32 accumulators per lane
+bool fused_supports_row_bytes(uint64_t row_bytes);
+
+cudaError_t launch_top(const QueryConst& qc, const TopPlan& tp, const uint32_t* d_t0, uint32_t smem_base,
+                       cudaStream_t st);
+cudaError_t launch_fused(const QueryConst& qc, const FusedPlan& fp, bool bits_mode, const uint32_t* d_t0,
+                         uint32_t smem_base, int num_sms, cudaStream_t st);
+// per-point evaluation (Evaluate2P): values (int64) and/or selection bits (bytes) for n points.
+// xs == nullptr means x = x_first + i.
+cudaError_t launch_eval_points(const QueryConst& qc, const uint64_t* xs, uint64_t x_first, uint64_t n,
+                               int64_t* values, uint8_t* bits, const uint32_t* d_t0, uint32_t smem_base,
+                               cudaStream_t st);
+// masked XOR of rows from a byte-per-row bit vector (any row_bytes multiple of 16)
+cudaError_t launch_scan_bytes(const uint8_t* db, uint64_t row_bytes, uint64_t n_rows, const uint8_t* bits,
+                              uint32_t* out, int num_sms, cudaStream_t st);
+cudaError_t launch_synth_fill(uint8_t* db, uint64_t slot_begin, uint64_t n_slots, uint32_t slot_bytes,
+                              uint32_t pitch, uint64_t seed, cudaStream_t st);
+cudaError_t probe_smem_base(uint32_t* out_base);
+cudaError_t configure_kernels();
+
+uint64_t launch_count();
+
+}  // namespace pirb
