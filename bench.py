@@ -1,0 +1,326 @@
+#!/usr/bin/env python
+"""bench.py — DPF-PIR answer throughput on B200 (BASELINE.json metric), one JSON line on rank 0.
+
+A step = one query answered over the whole database (one pass of the hot path).  Workload at every N:
+BASELINE.json configs[2], 2^24 rows x 256-byte slots (4 GiB), single query; at N > 1 the SAME
+database is row-sharded over the N GPUs (strong scaling) and the per-GPU partial answers are
+XOR-combined every step.
+
+  value     GB/s of database scanned per query with the database resident in HBM (device-timed)
+  e2e       the same through pir_answer() with HOST buffers: key in, answer out, sync per query
+  roofline  fused expand+scan kernel: N*S bytes per launch / its CUDA-event duration vs measured HBM
+  cpu_baseline / --impl reference: the CPU restatement of the reference's own algorithm
+            (per-row Evaluate2P + serial XOR, oracle/pir_oracle.c) on a bounded sample, all host threads
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+LOG_ROWS = int(os.environ.get("PIRB_BENCH_LOG_ROWS", "24"))
+SLOT_BYTES = int(os.environ.get("PIRB_BENCH_SLOT_BYTES", "256"))
+SEED = 2024
+CPU_SAMPLE_LOG_ROWS = 20
+METRIC = "dpf_pir_answer_db_scan_throughput"
+UNIT = "GB/s"
+
+
+def workload_name():
+    return "2^%d rows x %d-byte slots (%.1f GiB DB), single query, group size 1" % (
+        LOG_ROWS, SLOT_BYTES, (1 << LOG_ROWS) * SLOT_BYTES / 2**30)
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle is the timed thing here (the only place bench.py executes oracle/)
+# ------------------------------------------------------------------------------------------------
+def cpu_reference_run(steps, warmup):
+    import numpy as np
+    import oracle
+    cores = len(os.sched_getaffinity(0))
+    n = 1 << LOG_ROWS
+    rows = min(n, 1 << CPU_SAMPLE_LOG_ROWS)
+    nb = oracle.num_bits_for(n, 1, False)
+    data = oracle.synth_fill(SEED, 0, rows, SLOT_BYTES)
+    times = []
+    for i in range(warmup + steps):
+        o0, _ = oracle.gen_two_server(oracle.tape(SEED + i), nb, (i * 7919) % rows, 1)
+        t0 = time.perf_counter()
+        bits = oracle.expand_shared_query(o0, n, row_begin=0, n_rows=rows, nthreads=cores)  # db.go:110-174
+        oracle.answer_with_bits(data, SLOT_BYTES, 1, bits)                                   # db.go:75-107
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    ms = 1e3 * sum(times) / len(times)
+    gbs = rows * SLOT_BYTES / (ms * 1e-3) / 1e9
+    sample = "first 2^%d of 2^%d rows (%d MiB), %d-level per-row Evaluate2P + serial XOR, per step" % (
+        CPU_SAMPLE_LOG_ROWS, LOG_ROWS, rows * SLOT_BYTES >> 20, nb)
+    return gbs, ms, cores, sample
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    gbs, ms, cores, sample = cpu_reference_run(args.steps, args.warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": gbs, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": workload_name()},
+        "cpu_baseline": {"value": gbs, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": gbs, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "queries_per_s": 1e3 / (ms * (1 << LOG_ROWS) / min(1 << LOG_ROWS, 1 << CPU_SAMPLE_LOG_ROWS)),
+        "note": "Go toolchain absent: C restatement of the reference algorithm (oracle/), conservative (no Go allocs/goroutines)",
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks sampler
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows = []
+        self.proc = None
+        self.gpu = gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def gpu_arm(args):
+    import numpy as np
+    import torch
+    from pir_b200 import _capi
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit("WORLD_SIZE %d != --gpus %d" % (world, args.gpus))
+    L = _capi.lib()
+    if L.pir_device_count() <= local:
+        raise SystemExit("bench.py: no CUDA device for local rank %d (there is no CPU fallback)" % local)
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group(backend="nccl", device_id=torch.device("cuda", local))
+
+    n, S = 1 << LOG_ROWS, SLOT_BYTES
+    r0, r1 = rank * n // world, (rank + 1) * n // world
+    h = C.c_void_p()
+    _capi.check(L.pir_db_create(local, n, S, r0, r1 - r0, C.byref(h)))
+    _capi.check(L.pir_db_fill_synthetic(h, SEED))
+    nb = L.pir_num_bits_for(n, 1, 0)
+
+    total = args.warmup + args.steps
+    rng = np.random.default_rng(SEED)
+    idxs = [int(x) for x in rng.integers(0, n, size=total + 1)]
+    qs = (_capi.PirQuery * (2 * (total + 1)))()
+    for i, idx in enumerate(idxs):
+        tape = (C.c_uint8 * 97).from_buffer_copy(rng.integers(0, 256, size=97, dtype=np.uint8).tobytes())
+        _capi.check(L.pir_client_gen_two_server(nb, idx, 1, tape, C.byref(qs[2 * i]), C.byref(qs[2 * i + 1])))
+
+    stream = torch.cuda.Stream()
+    d_out = torch.zeros(S, dtype=torch.uint8, device="cuda")
+    gathered = torch.zeros(world * S, dtype=torch.uint8, device="cuda") if world > 1 else None
+    sp = C.c_void_p(stream.cuda_stream)
+
+    def step_device(i):
+        """one query, database resident, answer left on the device (combined on every rank)"""
+        _capi.check(L.pir_answer_batch_device(h, C.byref(qs[2 * i]), 1, C.c_void_p(d_out.data_ptr()), sp))
+        if world > 1:
+            with torch.cuda.stream(stream):
+                dist.all_gather_into_tensor(gathered, d_out)
+                comb = gathered.view(world, S)[0]
+                for g in range(1, world):
+                    comb = comb ^ gathered.view(world, S)[g]
+            return comb
+        return d_out
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- acceptance check (outside the timed region): both shares recover the queried slot ----
+    i = total
+    host = np.zeros(S, dtype=np.uint8)
+    acc = torch.zeros(S, dtype=torch.uint8, device="cuda")
+    for share in (0, 1):
+        _capi.check(L.pir_answer_batch_device(h, C.byref(qs[2 * i + share]), 1, C.c_void_p(d_out.data_ptr()), sp))
+        stream.synchronize()
+        acc ^= d_out
+    if world > 1:
+        allp = torch.zeros(world * S, dtype=torch.uint8, device="cuda")
+        dist.all_gather_into_tensor(allp, acc)
+        acc = allp.view(world, S)[0].clone()
+        for g in range(1, world):
+            acc ^= allp.view(world, S)[g]
+    if r0 <= idxs[i] < r1:
+        _capi.check(L.pir_db_download(h, idxs[i], host.ctypes.data_as(C.c_void_p), 1))
+        if not np.array_equal(acc.cpu().numpy(), host):
+            raise SystemExit("bench.py: recovered slot differs from the database slot — refusing to time a wrong path")
+
+    # ---- warm-up ----
+    for i in range(args.warmup):
+        step_device(i)
+    barrier()
+
+    # ---- device-resident timed region ----
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    _capi.check(L.pir_db_set_kernel_timing(h, 1))
+    launches0 = L.pir_kernel_launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record(stream)
+    for i in range(args.warmup, total):
+        step_device(i)
+    ev1.record(stream)
+    barrier()
+    dev_ms = ev0.elapsed_time(ev1)
+    launches = L.pir_kernel_launch_count() - launches0
+    kms, kcount = C.c_double(), C.c_uint64()
+    _capi.check(L.pir_db_get_kernel_timing(h, C.byref(kms), C.byref(kcount)))
+    _capi.check(L.pir_db_set_kernel_timing(h, 0))
+
+    # ---- end-to-end timed region: host buffers in, host answer out, every step ----
+    out_host = np.zeros(S, dtype=np.uint8)
+    comb_host = np.zeros(S, dtype=np.uint8)
+    for i in range(min(3, args.warmup)):
+        _capi.check(L.pir_answer(h, C.byref(qs[2 * i]), out_host.ctypes.data_as(C.c_void_p), S))
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.warmup, total):
+        _capi.check(L.pir_answer(h, C.byref(qs[2 * i]), out_host.ctypes.data_as(C.c_void_p), S))
+        if world > 1:
+            parts = [None] * world if rank == 0 else None
+            dist.gather_object(out_host.tobytes(), parts, dst=0)  # host reduction of N partial answers
+            if rank == 0:
+                comb_host[:] = 0
+                for p in parts:
+                    L.pir_xor_combine(comb_host.ctypes.data_as(C.c_void_p), p, S)
+    barrier()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    clocks = sampler.stop() if rank == 0 else None
+
+    if world > 1:
+        t = torch.tensor([dev_ms, e2e_ms, kms.value / max(1, kcount.value)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms, e2e_ms, k_avg_ms = [float(x) for x in t.cpu()]
+    else:
+        k_avg_ms = kms.value / max(1, kcount.value)
+
+    if rank == 0:
+        db_bytes = n * S
+        ms_step = dev_ms / args.steps
+        value = db_bytes / (ms_step * 1e-3) / 1e9
+        e2e_step = e2e_ms / args.steps
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        shard_bytes = (r1 - r0) * S
+        achieved = shard_bytes / (k_avg_ms * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": workload_name(), "sharding": "rows/%d" % world,
+                       "l2": "per-GPU shard (%d MiB) exceeds the 126 MB L2; every step scans all of it" % (shard_bytes >> 20),
+                       "combine": "none" if world == 1 else "all_gather of %d-byte partials + XOR" % S,
+                       "queries": "distinct seeded key per step, share 0"},
+            "queries_per_s": 1e3 / ms_step,
+            "e2e": {"value": db_bytes / (e2e_step * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": e2e_step,
+                    "h2d_bytes_per_step": C.sizeof(_capi.PirQuery), "d2h_bytes_per_step": S,
+                    "api": "pir_answer (C ABI, host key in / host answer out, stream sync per query)"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "kernel": "fused_kernel<1,false>", "kernel_ms": k_avg_ms,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650",
+                         "algorithmic_bytes_per_launch": shard_bytes,
+                         "aes_blocks_per_s": 3.0 * (r1 - r0) / (k_avg_ms * 1e-3)},
+            "clocks": clocks,
+        }
+        if world == 1:
+            gbs, ms, cores, sample = cpu_reference_run(3, 1)
+            line["cpu_baseline"] = {"value": gbs, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+        print(json.dumps(line), flush=True)
+    L.pir_db_destroy(h)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -148,6 +148,12 @@ void pir_xor_combine(void* acc, const void* part, size_t len);
 /* numBits as the server computes it (db.go:114-121): floor(log2(rows))+1, or 32 for keyword queries. */
 uint32_t pir_num_bits_for(uint64_t db_size, uint32_t group_size, int is_keyword);
 
+/* Per-launch timing of the dominant (fused expand+scan) kernel with CUDA events on the launching
+ * stream, for the roofline line of bench.py.  get() waits for the recorded launches, returns their
+ * summed duration and count, and resets the recorder. */
+int pir_db_set_kernel_timing(pir_db* db, int enable);
+int pir_db_get_kernel_timing(pir_db* db, double* total_ms, uint64_t* launches);
+
 /* counters for benchmarking: number of kernel launches issued by this library in this process */
 uint64_t pir_kernel_launch_count(void);
 

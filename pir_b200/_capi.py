@@ -30,6 +30,7 @@ EXPORTS = [
     "pir_answer", "pir_answer_batch", "pir_expand_bits", "pir_answer_with_bits",
     "pir_answer_batch_device", "pir_dpf_eval_points", "pir_xor_combine", "pir_num_bits_for",
     "pir_kernel_launch_count", "pir_client_gen_two_server",
+    "pir_db_set_kernel_timing", "pir_db_get_kernel_timing",
 ]
 
 
@@ -118,6 +119,8 @@ def lib():
     L.pir_num_bits_for.restype = C.c_uint32
     L.pir_kernel_launch_count.restype = C.c_uint64
     L.pir_client_gen_two_server.argtypes = [C.c_uint32, C.c_uint64, C.c_uint64, u8p, qp, qp]
+    L.pir_db_set_kernel_timing.argtypes = [vp, C.c_int]
+    L.pir_db_get_kernel_timing.argtypes = [vp, C.POINTER(C.c_double), u64p]
     L.pir_debug_round_keys.argtypes = [u8p, C.POINTER(C.c_uint32)]
     L.pir_debug_t0.argtypes = [C.POINTER(C.c_uint32)]
     if L.pir_abi_version() != 1:

@@ -209,6 +209,10 @@ struct pir_db {
     uint64_t out_cap = 0;
     uint8_t* h_out = nullptr;  // pinned
     uint64_t h_out_cap = 0;
+    // optional per-launch timing of the dominant (fused) kernel, for bench.py's roofline
+    bool timing = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pool;
+    size_t ev_used = 0;
 };
 
 namespace {
@@ -367,8 +371,37 @@ extern "C" int pir_db_destroy(pir_db* db) {
     if (db->h_out) cudaFreeHost(db->h_out);
     if (db->d_keywords) cudaFree(db->d_keywords);
     if (db->d_slots) cudaFree(db->d_slots);
+    for (auto& ev : db->ev_pool) {
+        cudaEventDestroy(ev.first);
+        cudaEventDestroy(ev.second);
+    }
     if (db->stream) cudaStreamDestroy(db->stream);
     delete db;
+    return PIR_OK;
+}
+
+extern "C" int pir_db_set_kernel_timing(pir_db* db, int enable) {
+    if (!db) return fail(PIR_ERR_BAD_ARG, "null handle");
+    std::lock_guard<std::mutex> lk(db->mu);
+    db->timing = enable != 0;
+    db->ev_used = 0;
+    return PIR_OK;
+}
+
+extern "C" int pir_db_get_kernel_timing(pir_db* db, double* total_ms, uint64_t* launches) {
+    if (!db || !total_ms || !launches) return fail(PIR_ERR_BAD_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(db->mu);
+    DeviceGuard g(db->device);
+    double sum = 0.0;
+    for (size_t i = 0; i < db->ev_used; i++) {
+        CU(cudaEventSynchronize(db->ev_pool[i].second));
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, db->ev_pool[i].first, db->ev_pool[i].second));
+        sum += ms;
+    }
+    *total_ms = sum;
+    *launches = db->ev_used;
+    db->ev_used = 0;
     return PIR_OK;
 }
 
@@ -506,7 +539,20 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
     fp.out = (uint32_t*)d_out;
     const bool fused = fused_supports_row_bytes(g.row_bytes) && !getenv("PIRB_FORCE_UNFUSED");
     if (fused) {
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (db->timing) {
+            if (db->ev_used == db->ev_pool.size()) {
+                CU(cudaEventCreate(&e0));
+                CU(cudaEventCreate(&e1));
+                db->ev_pool.emplace_back(e0, e1);
+            }
+            e0 = db->ev_pool[db->ev_used].first;
+            e1 = db->ev_pool[db->ev_used].second;
+            db->ev_used++;
+            CU(cudaEventRecord(e0, st));
+        }
         CU(launch_fused(qc, fp, false, ctx.d_t0, ctx.smem_base, ctx.num_sms, st));
+        if (e1) CU(cudaEventRecord(e1, st));
     } else {
         if ((rc = ensure_bits(db, g.n_rows))) return rc;
         fp.bits_out = db->d_bits;
