@@ -104,7 +104,7 @@ eval_points_kernel(const __grid_constant__ QueryConst qc, const uint64_t* __rest
 }
 
 // ------------------------------------------------------------------------------------------------
-// synthetic database (must match oracle orc_synth_word / orc_synth_fill)
+// synthetic database: the "pir_synth" generator of DESIGN.md (the test-suite checks it against its CPU twin)
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint64_t synth_word(uint64_t seed, uint64_t slot, uint32_t w) {
     uint64_t z = seed + slot * 0x9E3779B97F4A7C15ull + (uint64_t)w * 0xD1B54A32D192ED03ull;

@@ -1,0 +1,131 @@
+"""CPU tests of the product's host side: the C-ABI library loads and exports every symbol of
+include/pir_b200.h, host-only entry points agree with the oracle / golden vectors, and compute entry
+points FAIL LOUDLY without a CUDA device (there is no CPU fallback).  No kernel is launched here."""
+import ctypes as C
+import json
+import os
+import re
+
+import numpy as np
+import pytest
+
+import oracle
+from pir_b200 import _capi, sharding
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = json.load(open(os.path.join(ROOT, "tests", "golden", "dpf_pir_vectors.json")))
+
+
+def test_header_symbols_all_exported():
+    hdr = open(os.path.join(ROOT, "include", "pir_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(pir_[a-z0-9_]+)\s*\(", hdr))
+    assert declared, "no declarations parsed"
+    L = _capi.lib()
+    missing = [s for s in sorted(declared) if not hasattr(L, s)]
+    assert not missing, missing
+    assert declared == set(_capi.EXPORTS), declared ^ set(_capi.EXPORTS)
+    assert L.pir_abi_version() == 1
+
+
+def test_pod_layout_matches_oracle_pod():
+    assert C.sizeof(_capi.PirQuery) == C.sizeof(oracle.PirQuery) == 64 + 16 + 4 + 4 + 8 + 4 + 4 + 64 * 18
+    for (n1, _), (n2, _) in zip(_capi.PirQuery._fields_, oracle.PirQuery._fields_):
+        assert n1 == n2
+        assert getattr(_capi.PirQuery, n1).offset == getattr(oracle.PirQuery, n2).offset
+
+
+@pytest.mark.parametrize("case", GOLDEN["pir"] + GOLDEN["dpf"], ids=lambda c: c["name"])
+def test_client_keygen_matches_golden(case):
+    """pir_client_gen_two_server (dpf/client.go:17-150) reproduces the golden keys from the same tape."""
+    L = _capi.lib()
+    tape = (C.c_uint8 * 97).from_buffer_copy(bytes.fromhex(case["tape"]))
+    a = case.get("index", case.get("a"))
+    b = case.get("b", 1)
+    q0, q1 = _capi.PirQuery(), _capi.PirQuery()
+    _capi.check(L.pir_client_gen_two_server(case["num_bits"], a, b, tape, C.byref(q0), C.byref(q1)))
+    for q, want in ((q0, case["query0"]), (q1, case["query1"])):
+        q.group_size = case.get("group_size", 1)
+        assert q.to_bytes().hex() == want
+
+
+def test_client_keygen_random_tape_roundtrips_through_oracle():
+    L = _capi.lib()
+    q0, q1 = _capi.PirQuery(), _capi.PirQuery()
+    _capi.check(L.pir_client_gen_two_server(12, 3000, 1, None, C.byref(q0), C.byref(q1)))
+    xs = np.arange(4096, dtype=np.uint64)
+    s = oracle.evaluate2p(oracle.query_from_bytes(q0.to_bytes()), xs) + \
+        oracle.evaluate2p(oracle.query_from_bytes(q1.to_bytes()), xs)
+    assert s[3000] == 1 and np.count_nonzero(s) == 1
+
+
+def test_num_bits_for_matches_reference_rule():
+    L = _capi.lib()
+    for n in (1, 2, 3, 4, 1023, 1024, 1025, 1 << 20, (1 << 24) - 1, 1 << 24, 1 << 28):
+        for W in (1, 2, 3, 7):
+            if n // W == 0:
+                continue
+            assert L.pir_num_bits_for(n, W, 0) == (n // W).bit_length() == oracle.num_bits_for(n, W, False)
+            assert L.pir_num_bits_for(n, W, 1) == 32
+
+
+def test_round_keys_and_ttable_vs_fips197():
+    L = _capi.lib()
+    key = (C.c_uint8 * 16)(*bytes.fromhex("000102030405060708090a0b0c0d0e0f"))
+    rk = (C.c_uint32 * 44)()
+    L.pir_debug_round_keys(key, rk)
+    assert rk[43].to_bytes(4, "little").hex() == "4d2b30c5"  # FIPS-197 C.1 round[10].k_sch = 13111d7fe3944a17f307a78b4d2b30c5
+    orc = np.zeros(176, dtype=np.uint8)
+    oracle.lib().orc_aes128_expand_key(key, orc.ctypes.data_as(C.POINTER(C.c_uint8)))
+    assert np.array_equal(np.frombuffer(bytes(rk), dtype=np.uint8), orc)
+    t0 = (C.c_uint32 * 256)()
+    L.pir_debug_t0(t0)
+    assert t0[0] == 0xA56363C6 and t0[1] == 0x847C7CF8  # S(0)=0x63: [2s, s, s, 3s] little-endian
+
+
+def test_xor_combine():
+    rng = np.random.default_rng(0)
+    parts = [rng.integers(0, 256, size=777, dtype=np.uint8) for _ in range(5)]
+    want = parts[0] ^ parts[1] ^ parts[2] ^ parts[3] ^ parts[4]
+    assert np.array_equal(sharding.xor_combine(parts), want)
+    with pytest.raises(ValueError):
+        sharding.xor_combine([b"ab", b"abc"])
+
+
+def test_shard_slots_cover_database_exactly():
+    for n, W in ((1 << 24, 1), (1000, 3), (1024, 4), (7, 2), (5, 8), (12345, 64)):
+        for world in (1, 2, 3, 4, 8):
+            pos, rows = 0, 0
+            for r in range(world):
+                b, c = sharding.shard_slots(n, W, r, world)
+                assert b == pos and b % W == 0
+                assert c % W == 0 or r == world - 1
+                pos += c
+                rows += sharding.shard_rows(n, W, r, world)[1]
+            assert pos == n and rows == n // W
+
+
+@pytest.mark.skipif(_capi.lib().pir_device_count() > 0, reason="a CUDA device is present")
+def test_compute_entry_points_fail_loudly_without_gpu():
+    L = _capi.lib()
+    h = C.c_void_p()
+    rc = L.pir_db_create(0, 1024, 16, 0, 1024, C.byref(h))
+    assert rc == _capi.PIR_ERR_CUDA and not h.value
+    assert b"no CUDA device" in L.pir_last_error()
+    q = _capi.PirQuery.from_bytes(bytes.fromhex(GOLDEN["dpf"][1]["query0"]))
+    xs = (C.c_uint64 * 2)(0, 1)
+    out = (C.c_int64 * 2)()
+    assert L.pir_dpf_eval_points(0, C.byref(q), xs, 2, out) == _capi.PIR_ERR_CUDA
+    with pytest.raises(_capi.PirError):
+        _capi.check(L.pir_db_create(0, 1024, 16, 0, 1024, C.byref(h)))
+
+
+def test_product_never_imports_oracle():
+    """The oracle is test infrastructure: nothing under pir_b200/ may reference it."""
+    pkg = os.path.join(ROOT, "pir_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")) or f == "Makefile":
+                src = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in src and "from oracle" not in src, f
+                assert "pir_oracle" not in src and "orc_" not in src, f

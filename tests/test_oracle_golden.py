@@ -1,0 +1,155 @@
+"""CPU tests: the oracle (oracle/pir_oracle.c) against the committed golden vectors, FIPS-197, and the
+reference's own property tests re-expressed (dpf/dpf_test.go:11-107, db_test.go:18-64,
+slot_test.go:146-175).  No GPU, no product code on the compute path."""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+
+GOLDEN = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "dpf_pir_vectors.json")))
+
+
+def _u8(a):
+    return a.ctypes.data_as(C.POINTER(C.c_uint8))
+
+
+def test_aes_fips197_both_backends():
+    L = oracle.lib()
+    v = GOLDEN["aes_fips197_c1"]
+    key = np.frombuffer(bytes.fromhex(v["key"]), dtype=np.uint8).copy()
+    pt = np.frombuffer(bytes.fromhex(v["pt"]), dtype=np.uint8).copy()
+    for portable in (0, 1):
+        L.orc_aes_force_portable(portable)
+        rk = np.zeros(176, dtype=np.uint8)
+        ct = np.zeros(16, dtype=np.uint8)
+        L.orc_aes128_expand_key(_u8(key), _u8(rk))
+        L.orc_aes128_encrypt(_u8(rk), _u8(pt), _u8(ct))
+        assert ct.tobytes().hex() == v["ct"], portable
+        assert L.orc_aes_selftest() == 0
+    L.orc_aes_force_portable(0)
+
+
+def test_varint_edge_cases():
+    """encoding/binary.Varint on 8 bytes (dpf/server.go:95): zig-zag, early terminator, no terminator."""
+    L = oracle.lib()
+
+    def vi(b):
+        a = np.frombuffer(bytes(b), dtype=np.uint8).copy()
+        return L.orc_varint8(_u8(a))
+
+    assert vi([0] * 8) == 0
+    assert vi([1] + [0] * 7) == -1
+    assert vi([2] + [0] * 7) == 1
+    assert vi([0x7f] + [0xff] * 7) == -64
+    assert vi([0x80, 0x01] + [0] * 6) == 64          # ux = 128 -> 64
+    assert vi([0xff] * 8) == 0                       # no byte < 0x80: Uvarint returns (0, 0)
+    assert vi([0xff] * 7 + [0x7f]) == -(1 << 55)     # ux = 2^56 - 1 (odd) -> ^(ux >> 1)
+
+
+@pytest.mark.parametrize("case", GOLDEN["pir"], ids=lambda c: c["name"])
+def test_pir_golden(case):
+    tape = bytes.fromhex(case["tape"])
+    W, n, S = case["group_size"], case["db_size"], case["slot_bytes"]
+    assert oracle.num_bits_for(n, W, False) == case["num_bits"]
+    o0, o1 = oracle.gen_two_server(tape, case["num_bits"], case["index"], 1)
+    data = oracle.synth_fill(case["db_seed"], 0, n, S)
+    for share, o in enumerate((o0, o1)):
+        o.group_size = W
+        assert o.to_bytes().hex() == case["query%d" % share]
+        bits = oracle.expand_shared_query(o, n)
+        assert np.packbits(bits, bitorder="little").tobytes().hex() == case["bits%d_packed_le" % share]
+        assert np.array_equal(oracle.expand_tree(o, n), bits)
+        assert np.array_equal(oracle.expand_shared_query(o, n, nthreads=3), bits)
+        assert oracle.answer(o, data, n, S).tobytes().hex() == case["answer%d" % share]
+        assert oracle.answer(o, data, n, S, use_tree=True).tobytes().hex() == case["answer%d" % share]
+    rec = np.frombuffer(bytes.fromhex(case["answer0"]), dtype=np.uint8) ^ \
+        np.frombuffer(bytes.fromhex(case["answer1"]), dtype=np.uint8)
+    want = data[case["index"] * W:(case["index"] + 1) * W].reshape(-1)
+    assert np.array_equal(rec, want)
+
+
+@pytest.mark.parametrize("case", GOLDEN["dpf"], ids=lambda c: c["name"])
+def test_dpf_golden(case):
+    o0, o1 = oracle.gen_two_server(bytes.fromhex(case["tape"]), case["num_bits"], case["a"], case["b"])
+    xs = np.array(case["points"], dtype=np.uint64)
+    for share, o in enumerate((o0, o1)):
+        assert o.to_bytes().hex() == case["query%d" % share]
+        assert oracle.evaluate2p(o, xs).tolist() == case["values%d" % share]
+
+
+def test_xor_slots_reference_vectors():
+    """slot_test.go:146-175 through answer_with_bits (XorSlots is its inner loop, slot.go:19-30)."""
+    for v in GOLDEN["xor_slots"]:
+        slots = np.frombuffer(bytes.fromhex(v["a"]) + bytes.fromhex(v["b"]), dtype=np.uint8)
+        out = oracle.answer_with_bits(slots, 4, 1, np.array([1, 1], dtype=np.uint8))
+        assert out.tobytes().hex() == v["out"]
+
+
+def test_correct_two_server_property():
+    """dpf/dpf_test.go:11-39: ans0 + ans1 == b at a, 0 elsewhere, over whole random domains."""
+    rng = np.random.default_rng(5)
+    for trial in range(40):
+        num = int(rng.integers(100, 1124))
+        nb = num.bit_length()
+        a, b = int(rng.integers(0, num)), int(rng.integers(1, 1000))
+        o0, o1 = oracle.gen_two_server(oracle.tape(9000 + trial), nb, a, b)
+        xs = np.arange(num, dtype=np.uint64)
+        s = oracle.evaluate2p(o0, xs) + oracle.evaluate2p(o1, xs)
+        want = np.zeros(num, dtype=np.int64)
+        want[a] = b
+        assert np.array_equal(s, want)
+
+
+def test_point_function_parity_property_keyword_domain():
+    """dpf/dpf_test.go:41-107: parity XOR is the point function, also on sparse 64-bit points."""
+    rng = np.random.default_rng(6)
+    for nb in (32, 64):
+        a = int(rng.integers(0, 1 << 62)) & ((1 << nb) - 1)
+        o0, o1 = oracle.gen_two_server(oracle.tape(700 + nb), nb, a, 1)
+        xs = np.concatenate([rng.integers(0, 1 << 62, size=200, dtype=np.uint64) & np.uint64((1 << nb) - 1),
+                             np.array([a], dtype=np.uint64)])
+        p = (np.abs(oracle.evaluate2p(o0, xs)) % 2) ^ (np.abs(oracle.evaluate2p(o1, xs)) % 2)
+        assert np.array_equal(p, (xs == np.uint64(a)).astype(np.int64))
+
+
+def test_shared_query_property():
+    """db_test.go:18-64 (TestSharedQuery): 2^10 x 3 B, group sizes 1..4, recover == slots."""
+    n, S = 1024, 3
+    data = oracle.synth_fill(11, 0, n, S)
+    rng = np.random.default_rng(7)
+    for W in (1, 2, 3, 4):
+        h = n // W
+        for trial in range(6):
+            idx = int(rng.integers(0, h))
+            o0, o1 = oracle.gen_two_server(oracle.tape(100 * W + trial), oracle.num_bits_for(n, W), idx, 1)
+            o0.group_size = o1.group_size = W
+            rec = oracle.answer(o0, data, n, S, nthreads=4) ^ oracle.answer(o1, data, n, S, use_tree=True)
+            assert np.array_equal(rec, data[idx * W:(idx + 1) * W].reshape(-1))
+
+
+def test_keyword_database_query():
+    """IsKeywordBased evaluation over db.Keywords (db.go:119-121,132-135): numBits = 32."""
+    n, S = 300, 16
+    rng = np.random.default_rng(8)
+    kw = np.sort(rng.choice(1 << 32, size=n, replace=False).astype(np.uint64))
+    data = oracle.synth_fill(12, 0, n, S)
+    target = 123
+    o0, o1 = oracle.gen_two_server(oracle.tape(55), 32, int(kw[target]), 1)
+    o0.is_keyword = o1.is_keyword = 1
+    rec = oracle.answer(o0, data, n, S, keywords=kw) ^ oracle.answer(o1, data, n, S, keywords=kw)
+    assert np.array_equal(rec, data[target])
+    bits = oracle.expand_shared_query(o0, n, keywords=kw) ^ oracle.expand_shared_query(o1, n, keywords=kw)
+    assert bits.sum() == 1 and bits[target] == 1
+
+
+def test_row_range_expansion_matches_full():
+    n = 5000
+    o0, _ = oracle.gen_two_server(oracle.tape(3), oracle.num_bits_for(n), 4321, 1)
+    full = oracle.expand_shared_query(o0, n)
+    for r0, cnt in ((0, 1), (17, 1000), (4096, 904), (4999, 1)):
+        assert np.array_equal(oracle.expand_tree(o0, n, r0, cnt), full[r0:r0 + cnt])
+        assert np.array_equal(oracle.expand_shared_query(o0, n, row_begin=r0, n_rows=cnt), full[r0:r0 + cnt])
