@@ -1,0 +1,107 @@
+// aes_unrolled.cuh — the hot-loop form of the PRG node expansion (dpf/common.go:62-75 +
+// dpf/server.go:68-92): all AES rounds unrolled so that every round-key word is a constant-bank
+// operand of the LOP3 that consumes it (no LDC, no register moves), and only the table lookups whose
+// output bytes are actually used downstream are issued:
+//
+//   block 0 (sL):            rounds 1-9 full, last round 16 lookups (8 at a leaf parent)
+//   block 1 (tL, sR[0:15]):  rounds 1-9 full, last round 16 lookups (9 at a leaf parent)
+//   block 2 (sR[15], tR):    rounds 1-8 full, round 9 columns 0,1 only (column 1 at a leaf parent),
+//                            last round 2 lookups (1 at a leaf parent)
+//
+// 458 lookups for an inner node, 438 for a leaf parent (a full 3-block PRG is 480).
+#pragma once
+#include "dpf_device.cuh"
+
+namespace pirb {
+
+// state after round 9 for blocks 0,1 and after round 8 for block 2
+__device__ __forceinline__ void aes3_main_rounds(const QueryConst& qc, const uint32_t s[4], uint32_t lc,
+                                                 uint32_t a[3][4]) {
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+#pragma unroll
+        for (int c = 0; c < 4; c++) a[k][c] = s[c] ^ qc.rk[k][c];
+#pragma unroll
+    for (int r = 1; r <= 8; r++) {
+        uint32_t n[3][4];
+#pragma unroll
+        for (int k = 0; k < 3; k++) aes_round(a[k], n[k], &qc.rk[k][4 * r], lc);
+#pragma unroll
+        for (int k = 0; k < 3; k++)
+#pragma unroll
+            for (int c = 0; c < 4; c++) a[k][c] = n[k][c];
+    }
+    {
+        uint32_t n[2][4];
+#pragma unroll
+        for (int k = 0; k < 2; k++) aes_round(a[k], n[k], &qc.rk[k][36], lc);
+#pragma unroll
+        for (int k = 0; k < 2; k++)
+#pragma unroll
+            for (int c = 0; c < 4; c++) a[k][c] = n[k][c];
+    }
+}
+
+// one column of a middle round
+__device__ __forceinline__ uint32_t aes_round_col(const uint32_t a[4], int c, uint32_t rkw, uint32_t lc) {
+    uint32_t v0 = lds0(__byte_perm(a[c], lc, 0x7604));
+    uint32_t v1 = lds0(__byte_perm(a[(c + 1) & 3], lc, 0x7615));
+    uint32_t v2 = lds1(__byte_perm(a[(c + 2) & 3], lc, 0x7624));
+    uint32_t v3 = lds1(__byte_perm(a[(c + 3) & 3], lc, 0x7635));
+    return v0 ^ v1 ^ v2 ^ v3 ^ rkw;
+}
+
+// S-box of byte 0 of x, delivered in byte 0 (T2 = [s,3s,2s,s]); of byte 1 of x in byte 1 (T3 = [s,s,3s,2s])
+__device__ __forceinline__ uint32_t sbox_b0(uint32_t x, uint32_t lc) { return lds1(__byte_perm(x, lc, 0x7604)); }
+__device__ __forceinline__ uint32_t sbox_b1(uint32_t x, uint32_t lc) { return lds1(__byte_perm(x, lc, 0x7615)); }
+
+// Inner node: both children in full, from the state left by aes3_main_rounds.
+__device__ __forceinline__ void inner_tail(const QueryConst& qc, const uint32_t a[3][4], const uint32_t s[4],
+                                           uint32_t t, const uint32_t cw[4], uint32_t cwtl, uint32_t cwtr,
+                                           uint32_t lc, Children& out) {
+    const uint32_t n20 = aes_round_col(a[2], 0, qc.rk[2][36], lc);
+    const uint32_t n21 = aes_round_col(a[2], 1, qc.rk[2][37], lc);
+    uint32_t b0[4], b1[4];
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        b0[c] = aes_last_word(a[0], c, qc.rk[0][40 + c], s[c], lc);
+        b1[c] = aes_last_word(a[1], c, qc.rk[1][40 + c], s[c], lc);
+    }
+    // block 2, bytes 0 and 1 of word 0 only
+    const uint32_t u0 = sbox_b0(n20, lc), u1 = sbox_b1(n21, lc);
+    const uint32_t b2 = ((u0 & 0xffu) | (u1 & 0xff00u)) ^ qc.rk[2][40] ^ s[0];
+    const uint32_t m = 0u - t;
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        const uint32_t nxt = (c < 3) ? b1[c + 1] : b2;
+        const uint32_t cwc = cw[c] & m;
+        out.sl[c] = b0[c] ^ cwc;
+        out.sr[c] = __funnelshift_r(b1[c], nxt, 8) ^ cwc;
+    }
+    out.tl = (b1[0] & 1u) ^ (t & cwtl);
+    out.tr = ((b2 >> 8) & 1u) ^ (t & cwtr);
+}
+
+// Leaf parent: only what the two selection bits need (8 seed bytes and t of each child).
+// Returns bit0 = selection bit of the left leaf, bit1 = of the right leaf.
+__device__ __forceinline__ uint32_t leaf_parent_tail(const QueryConst& qc, const uint32_t a[3][4],
+                                                     const uint32_t s[4], uint32_t t, const uint32_t cw[4],
+                                                     uint32_t cwtl, uint32_t cwtr, uint32_t lc) {
+    const uint32_t n21 = aes_round_col(a[2], 1, qc.rk[2][37], lc);
+    const uint32_t l0 = aes_last_word(a[0], 0, qc.rk[0][40], s[0], lc);
+    const uint32_t l1 = aes_last_word(a[0], 1, qc.rk[0][41], s[1], lc);
+    const uint32_t r0 = aes_last_word(a[1], 0, qc.rk[1][40], s[0], lc);
+    const uint32_t r1 = aes_last_word(a[1], 1, qc.rk[1][41], s[1], lc);
+    const uint32_t r2 = sbox_b0(a[1][2], lc) ^ qc.rk[1][42] ^ s[2];          // byte 0 valid
+    const uint32_t b2 = sbox_b1(n21, lc) ^ qc.rk[2][40] ^ s[0];              // byte 1 valid
+    const uint32_t m = 0u - t;
+    const uint32_t c0 = cw[0] & m, c1 = cw[1] & m;
+    const uint32_t sl0 = l0 ^ c0, sl1 = l1 ^ c1;
+    const uint32_t sr0 = __funnelshift_r(r0, r1, 8) ^ c0;
+    const uint32_t sr1 = __funnelshift_r(r1, r2, 8) ^ c1;
+    const uint32_t tl = (r0 & 1u) ^ (t & cwtl);
+    const uint32_t tr = ((b2 >> 8) & 1u) ^ (t & cwtr);
+    return leaf_select_bit(sl0, sl1, tl, qc.fcw_parity) | (leaf_select_bit(sr0, sr1, tr, qc.fcw_parity) << 1);
+}
+
+}  // namespace pirb

@@ -295,13 +295,13 @@ struct Plan {
 };
 
 // Choose the per-thread depth D and CTA breadth B (kernels.cuh) for a shard of rows.
-Plan make_plan(uint32_t nb, uint64_t first_row, uint64_t n_rows, int num_sms) {
+Plan make_plan(uint32_t nb, uint64_t first_row, uint64_t n_rows, int num_sms, int max_depth = kMaxDfsDepth) {
     Plan best{};
     double best_score = -1.0;
     uint32_t Bmax = nb - 1 < (uint32_t)kFusedLogThreads ? nb - 1 : (uint32_t)kFusedLogThreads;
     int forced = -1;
     if (const char* e = getenv("PIRB_DFS_DEPTH")) forced = atoi(e);
-    for (int D = kMaxDfsDepth; D >= 0; D--) {
+    for (int D = max_depth; D >= 0; D--) {
         if ((uint32_t)D + Bmax > nb - 1) continue;
         if (forced >= 0 && D != forced && (uint32_t)forced + Bmax <= nb - 1) continue;
         uint32_t B = Bmax;
@@ -511,6 +511,38 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
         CU(launch_eval_points(qc, db->d_keywords + (g.first_row - db->slot_begin), 0, g.n_rows, nullptr,
                               db->d_bits, ctx.d_t0, ctx.smem_base, st));
         CU(launch_scan_bytes(db->d_slots, g.row_bytes, g.n_rows, db->d_bits, (uint32_t*)d_out, ctx.num_sms, st));
+        return PIR_OK;
+    }
+    static const bool use_v1 = getenv("PIRB_KERNEL") && !strcmp(getenv("PIRB_KERNEL"), "v1");
+    if (!use_v1 && answer_kernel_supports(g.row_bytes, 0)) {
+        // warp-specialised kernel: walks the top of the tree itself, one launch per query
+        Plan p4 = make_plan(g.nb, g.first_row, g.n_rows, ctx.num_sms, 4);
+        AnswerPlan ap{};
+        ap.db = db->d_slots;
+        ap.row_bytes = g.row_bytes;
+        ap.first_row = g.first_row;
+        ap.n_rows = g.n_rows;
+        ap.D = p4.D;
+        ap.B = p4.B;
+        ap.Fc = p4.Fc;
+        ap.task_first = p4.task_first;
+        ap.task_count = p4.task_count;
+        ap.out = (uint32_t*)d_out;
+        if (const char* dbg = getenv("PIRB_DEBUG_FLAGS")) ap.pad = (uint32_t)atoi(dbg);  // timing experiments only
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (db->timing) {
+            if (db->ev_used == db->ev_pool.size()) {
+                CU(cudaEventCreate(&e0));
+                CU(cudaEventCreate(&e1));
+                db->ev_pool.emplace_back(e0, e1);
+            }
+            e0 = db->ev_pool[db->ev_used].first;
+            e1 = db->ev_pool[db->ev_used].second;
+            db->ev_used++;
+            CU(cudaEventRecord(e0, st));
+        }
+        CU(launch_answer(qc, ap, ctx.d_t0, ctx.smem_base, ctx.num_sms, st));
+        if (e1) CU(cudaEventRecord(e1, st));
         return PIR_OK;
     }
     Plan p = make_plan(g.nb, g.first_row, g.n_rows, ctx.num_sms);

@@ -18,6 +18,7 @@ namespace pirb {
 
 static std::atomic<uint64_t> g_launches{0};
 uint64_t launch_count() { return g_launches.load(); }
+void count_launch() { g_launches++; }
 
 extern __shared__ __align__(16) uint8_t g_smem[];
 
@@ -426,7 +427,7 @@ cudaError_t configure_kernels() {
     if ((e = set_max_smem(fused_kernel<N, true>)) != cudaSuccess) return e;
     PIRB_CFG(1) PIRB_CFG(2) PIRB_CFG(4) PIRB_CFG(8)
 #undef PIRB_CFG
-    return cudaSuccess;
+    return configure_answer_kernel();
 }
 
 cudaError_t launch_top(const QueryConst& qc, const TopPlan& tp, const uint32_t* d_t0, uint32_t smem_base,

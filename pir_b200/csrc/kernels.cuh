@@ -30,6 +30,19 @@ struct FusedPlan {
     uint8_t* bits_out;        // BITS mode: one byte per shard row
 };
 
+// Geometry of one launch of the warp-specialised answer kernel (answer_kernel.cu).  Same meaning as
+// FusedPlan, but the kernel walks the top of the tree itself (no frontier buffers).
+struct AnswerPlan {
+    const uint8_t* db;
+    uint64_t row_bytes;   // power of two, 16..512
+    uint64_t first_row;
+    uint64_t n_rows;
+    uint32_t D, B, Fc, pad;
+    uint64_t task_first;
+    uint64_t task_count;
+    uint32_t* out;        // row_bytes/4 words, zeroed before launch (atomic XOR)
+};
+
 struct TopPlan {
     uint32_t Fc;          // produce nodes of level Fc
     uint32_t pad;
@@ -62,6 +75,13 @@ cudaError_t launch_synth_fill(uint8_t* db, uint64_t slot_begin, uint64_t n_slots
 cudaError_t probe_smem_base(uint32_t* out_base);
 cudaError_t configure_kernels();
 
+// warp-specialised fused expand+scan kernel (answer_kernel.cu)
+bool answer_kernel_supports(uint64_t row_bytes, uint32_t D);
+cudaError_t configure_answer_kernel();
+cudaError_t launch_answer(const QueryConst& qc, const AnswerPlan& ap, const uint32_t* d_t0, uint32_t smem_base,
+                          int num_sms, cudaStream_t st);
+
 uint64_t launch_count();
+void count_launch();
 
 }  // namespace pirb
