@@ -62,6 +62,86 @@ __device__ __forceinline__ uint32_t range_mask32(uint64_t rowbase, uint32_t rw, 
     return hi & ~lo;
 }
 
+// ---- scan: selected rows of 32 words -> registers -------------------------------------------------
+struct ScanLane {
+    uint32_t rpl, h, c;
+    const uint8_t* lane_db;  // db + this lane's 16-byte chunk
+};
+
+__device__ __forceinline__ ScanLane scan_lane(const AnswerPlan& ap) {
+    ScanLane sl;
+    const uint32_t lane = threadIdx.x & 31u;
+    sl.c = (uint32_t)(ap.row_bytes >> 4);  // 16-byte chunks per row, power of two <= 32
+    const uint32_t logc = 31u - __clz(sl.c);
+    sl.rpl = 32u >> logc;                  // rows per warp load
+    sl.h = lane >> logc;
+    sl.lane_db = ap.db + ((lane & (sl.c - 1u)) << 4);
+    return sl;
+}
+
+// XOR the selected rows of words [g*32, g*32+32) of one task buffer into acc.  `list` is a private
+// 2 KB scratch of the calling warp.
+template <int UNROLL>
+__device__ __forceinline__ void scan_group(const AnswerPlan& ap, const ScanLane& sl, const uint32_t* wbuf,
+                                           uint32_t g, uint64_t p, uint16_t* list, uint4& acc) {
+    const uint32_t lane = threadIdx.x & 31u, rows_log = ap.D + 1;
+    // byte address of task row 0; rows before first_row are never selected
+    const int64_t task_row0 = (int64_t)((p << ap.B) << rows_log) - (int64_t)ap.first_row;
+    const uint8_t* tbase = sl.lane_db + task_row0 * (int64_t)ap.row_bytes;
+    const uint32_t widx = g * 32u + lane;
+    uint32_t w = wbuf[widx];
+    const uint32_t cnt = __popc(w);
+    uint32_t pre = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, pre, o);
+        if (lane >= (uint32_t)o) pre += v;
+    }
+    const uint32_t total = __shfl_sync(0xffffffffu, pre, 31);
+    uint32_t pos = pre - cnt;
+    const uint32_t rbase = widx << rows_log;
+    while (w) {
+        list[pos++] = (uint16_t)(rbase + (uint32_t)__ffs(w) - 1u);
+        w &= w - 1u;
+    }
+    __syncwarp();
+    for (uint32_t e0 = 0; e0 < ((ap.pad & 1u) ? 0u : total); e0 += sl.rpl * UNROLL) {
+        uint4 v[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; u++) {
+            const uint32_t e = e0 + u * sl.rpl + sl.h;
+            v[u] = make_uint4(0, 0, 0, 0);
+            if (e < total) v[u] = ldg_nc_v4(tbase + (uint64_t)list[e] * ap.row_bytes);
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; u += 2) {
+            acc.x ^= v[u].x ^ v[u + 1].x; acc.y ^= v[u].y ^ v[u + 1].y;
+            acc.z ^= v[u].z ^ v[u + 1].z; acc.w ^= v[u].w ^ v[u + 1].w;
+        }
+    }
+    __syncwarp();
+}
+
+// fold the sub-rows of a warp load, then XOR into the CTA's shared accumulator
+__device__ __forceinline__ void fold_acc(const ScanLane& sl, uint4 acc) {
+    const uint32_t lane = threadIdx.x & 31u;
+    for (uint32_t off = 16; off >= sl.c && off > 0; off >>= 1) {
+        acc.x ^= __shfl_xor_sync(0xffffffffu, acc.x, off);
+        acc.y ^= __shfl_xor_sync(0xffffffffu, acc.y, off);
+        acc.z ^= __shfl_xor_sync(0xffffffffu, acc.z, off);
+        acc.w ^= __shfl_xor_sync(0xffffffffu, acc.w, off);
+    }
+    uint32_t* red = reinterpret_cast<uint32_t*>(g_smem2 + kOffRed);
+    if (lane < sl.c && (acc.x | acc.y | acc.z | acc.w)) {
+        atomicXor(&red[lane * 4 + 0], acc.x);
+        atomicXor(&red[lane * 4 + 1], acc.y);
+        atomicXor(&red[lane * 4 + 2], acc.z);
+        atomicXor(&red[lane * 4 + 3], acc.w);
+    }
+}
+
+constexpr uint32_t kGroups = kTreeThreads / 32;  // 32-word groups per task
+
 // ---- tree role ------------------------------------------------------------------------------------
 __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan& ap, uint32_t lc) {
     const uint32_t tid = threadIdx.x, warp = tid >> 5;
@@ -174,6 +254,17 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
         words[buf * kTreeThreads + tid] = word;
         __threadfence_block();
         bar_arrive(BAR_FULL0 + buf, kAnswerThreads);
+        if (k + 1 == k1) {
+            // last task of this CTA: nothing left to expand, so the tree warps scan groups
+            // [kScanWarps, kGroups) themselves (row lists in the now idle sibling stack)
+            bar_sync(BAR_TREE, kTreeThreads);
+            const ScanLane sl = scan_lane(ap);
+            uint4 acc = make_uint4(0, 0, 0, 0);
+            uint16_t* list = reinterpret_cast<uint16_t*>(g_smem2 + kOffStack) + warp * kListEntries;
+            for (uint32_t g = kScanWarps + warp; g < kGroups; g += kTreeThreads / 32)
+                scan_group<8>(ap, sl, words + buf * kTreeThreads, g, p, list, acc);
+            fold_acc(sl, acc);
+        }
     }
     // drain the scan warps' last "empty" arrivals so that no barrier is left half-complete
     const uint32_t ntask = (uint32_t)(k1 - k0);
@@ -182,91 +273,26 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
 }
 
 // ---- scan role ------------------------------------------------------------------------------------
-template <int UNROLL>
 __device__ __forceinline__ void scan_role(const AnswerPlan& ap) {
-    const uint32_t lane = threadIdx.x & 31u, sw = (threadIdx.x - kTreeThreads) >> 5;
-    const uint32_t B = ap.B, rows_log = ap.D + 1;
-    const uint32_t c = (uint32_t)(ap.row_bytes >> 4);        // 16-byte chunks per row, power of two <= 32
-    const uint32_t logc = 31u - __clz(c);
-    const uint32_t rpl = 32u >> logc;                        // rows per warp load
-    const uint32_t h = lane >> logc, chunk = lane & (c - 1u);
+    const uint32_t sw = (threadIdx.x - kTreeThreads) >> 5;
+    const ScanLane sl = scan_lane(ap);
     const uint32_t* words = reinterpret_cast<const uint32_t*>(g_smem2 + kOffWords);
-    // the row lists live above the tables
-    uint32_t dyn_base = smem_addr(g_smem2);
-    uint16_t* list = reinterpret_cast<uint16_t*>(g_smem2 + (kTableEnd - dyn_base)) + sw * kListEntries;
-    const uint32_t wpw = kTreeThreads / kScanWarps;          // words per scan warp per task
+    const uint32_t dyn_base = smem_addr(g_smem2);
+    uint16_t* list = reinterpret_cast<uint16_t*>(g_smem2 + (kTableEnd - dyn_base)) + sw * kListEntries;  // above the tables
     uint4 acc = make_uint4(0, 0, 0, 0);
-
     const uint64_t k0 = (uint64_t)blockIdx.x * ap.task_count / gridDim.x;
     const uint64_t k1 = (uint64_t)(blockIdx.x + 1) * ap.task_count / gridDim.x;
     for (uint64_t k = k0; k < k1; k++) {
         const uint32_t buf = (uint32_t)(k - k0) & 1u;
-        const uint64_t p = ap.task_first + k;
         bar_sync(BAR_FULL0 + buf, kAnswerThreads);
-        // byte address of (task row 0, this lane's chunk); rows before first_row are never selected
-        const int64_t task_row0 = (int64_t)((p << B) << rows_log) - (int64_t)ap.first_row;
-        const uint8_t* tbase = ap.db + task_row0 * (int64_t)ap.row_bytes + (chunk << 4);
-        for (uint32_t g = 0; g < wpw; g += 32) {
-            // -- compact list of the selected rows of 32 words (row offsets inside the task) --
-            const uint32_t widx = sw * wpw + g + lane;
-            uint32_t w = words[buf * kTreeThreads + widx];
-            const uint32_t cnt = __popc(w);
-            uint32_t pre = cnt;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const uint32_t v = __shfl_up_sync(0xffffffffu, pre, o);
-                if (lane >= (uint32_t)o) pre += v;
-            }
-            const uint32_t total = __shfl_sync(0xffffffffu, pre, 31);
-            uint32_t pos = pre - cnt;
-            const uint32_t rbase = widx << rows_log;
-            while (w) {
-                list[pos++] = (uint16_t)(rbase + (uint32_t)__ffs(w) - 1u);
-                w &= w - 1u;
-            }
-            __syncwarp();
-            // -- stream the selected rows: rpl rows per warp load --
-            for (uint32_t e0 = 0; e0 < ((ap.pad & 1u) ? 0u : total); e0 += rpl * UNROLL) {
-                uint4 v[UNROLL];
-#pragma unroll
-                for (int u = 0; u < UNROLL; u++) {
-                    const uint32_t e = e0 + u * rpl + h;
-                    v[u] = make_uint4(0, 0, 0, 0);
-                    if (e < total) v[u] = ldg_nc_v4(tbase + (uint64_t)list[e] * ap.row_bytes);
-                }
-#pragma unroll
-                for (int u = 0; u < UNROLL; u += 2) {
-                    acc.x ^= v[u].x ^ v[u + 1].x; acc.y ^= v[u].y ^ v[u + 1].y;
-                    acc.z ^= v[u].z ^ v[u + 1].z; acc.w ^= v[u].w ^ v[u + 1].w;
-                }
-            }
-            __syncwarp();
-        }
+        // the tree warps help with the CTA's last task (they have nothing left to expand): groups
+        // [0, kScanWarps) stay here, the rest is theirs
+        const uint32_t gend = (k + 1 == k1) ? (uint32_t)kScanWarps : kGroups;
+        for (uint32_t g = sw; g < gend; g += kScanWarps)
+            scan_group<16>(ap, sl, words + buf * kTreeThreads, g, ap.task_first + k, list, acc);
         bar_arrive(BAR_EMPTY0 + buf, kAnswerThreads);
     }
-
-    // reduce: sub-rows of a warp load, then the scan warps of the CTA, then one atomic per word
-    for (uint32_t off = 16; off >= c && off > 0; off >>= 1) {
-        acc.x ^= __shfl_xor_sync(0xffffffffu, acc.x, off);
-        acc.y ^= __shfl_xor_sync(0xffffffffu, acc.y, off);
-        acc.z ^= __shfl_xor_sync(0xffffffffu, acc.z, off);
-        acc.w ^= __shfl_xor_sync(0xffffffffu, acc.w, off);
-    }
-    uint32_t* red = reinterpret_cast<uint32_t*>(g_smem2 + kOffRed);
-    const uint32_t st = threadIdx.x - kTreeThreads;
-    for (uint32_t i = st; i < 4u * c; i += 32u * kScanWarps) red[i] = 0;
-    bar_sync(BAR_SCAN, 32 * kScanWarps);
-    if (lane < c) {
-        atomicXor(&red[lane * 4 + 0], acc.x);
-        atomicXor(&red[lane * 4 + 1], acc.y);
-        atomicXor(&red[lane * 4 + 2], acc.z);
-        atomicXor(&red[lane * 4 + 3], acc.w);
-    }
-    bar_sync(BAR_SCAN, 32 * kScanWarps);
-    for (uint32_t i = st; i < 4u * c; i += 32u * kScanWarps) {
-        const uint32_t v = red[i];
-        if (v) atomicXor(&ap.out[i], v);
-    }
+    fold_acc(sl, acc);
 }
 
 __global__ void __launch_bounds__(kAnswerThreads, 1)
@@ -279,11 +305,19 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
         if (base + dyn < kTableEnd + kListBytes || base + kScratchEnd > kTableBase) __trap();
     }
     fill_tables(t0);
+    uint32_t* red = reinterpret_cast<uint32_t*>(g_smem2 + kOffRed);
+    if (threadIdx.x < 128) red[threadIdx.x] = 0;
     __syncthreads();
     if (threadIdx.x < kTreeThreads)
         tree_role(qc, ap, lane_const());
     else
-        scan_role<16>(ap);
+        scan_role(ap);
+    __syncthreads();
+    const uint32_t words_out = (uint32_t)(ap.row_bytes >> 2);
+    if (threadIdx.x < words_out) {
+        const uint32_t v = red[threadIdx.x];
+        if (v) atomicXor(&ap.out[threadIdx.x], v);
+    }
 }
 
 bool answer_kernel_supports(uint64_t row_bytes, uint32_t D) {
