@@ -142,6 +142,51 @@ __device__ __forceinline__ void fold_acc(const ScanLane& sl, uint4 acc) {
 
 constexpr uint32_t kGroups = kTreeThreads / 32;  // 32-word groups per task
 
+// ---- cooperative node expansion for the narrow top of a task --------------------------------------
+// One warp executing a whole 3-block PRG is bound by its own SMSP's ALU rate (~2500 cycles per level).
+// Near the root only a few nodes exist, so three warps on three SMSPs each take ONE AES block of the
+// same node and write their part of the children straight into shared memory:
+//   block 0 -> sL;  block 1 -> tL and bytes 0..14 of sR;  block 2 -> byte 15 of sR and tR.
+__device__ __forceinline__ void coop_block(const QueryConst& qc, uint32_t k, uint4 sv, uint32_t t, uint32_t level,
+                                           uint32_t lc, uint8_t* left_s, uint8_t* left_t, uint8_t* right_s,
+                                           uint8_t* right_t) {
+    const uint32_t s[4] = {sv.x, sv.y, sv.z, sv.w};
+    uint32_t a[4], n[4], o[4];
+#pragma unroll
+    for (int c = 0; c < 4; c++) a[c] = s[c] ^ qc.rk[k][c];
+#pragma unroll 1
+    for (int r = 1; r <= 9; r++) {
+        aes_round(a, n, &qc.rk[k][4 * r], lc);
+#pragma unroll
+        for (int c = 0; c < 4; c++) a[c] = n[c];
+    }
+#pragma unroll
+    for (int c = 0; c < 4; c++) o[c] = aes_last_word(a, c, qc.rk[k][40 + c], s[c], lc);
+    const uint32_t m = 0u - t;
+    uint32_t cw[4];
+#pragma unroll
+    for (int c = 0; c < 4; c++) cw[c] = qc.cw[level][c] & m;
+    if (k == 0) {
+        if (left_s) *reinterpret_cast<uint4*>(left_s) = make_uint4(o[0] ^ cw[0], o[1] ^ cw[1], o[2] ^ cw[2], o[3] ^ cw[3]);
+    } else if (k == 1) {
+        if (left_t) *left_t = (uint8_t)((o[0] & 1u) ^ (t & (uint32_t)(qc.cw_tl >> level) & 1u));
+        if (right_s) {
+            uint32_t* rs = reinterpret_cast<uint32_t*>(right_s);
+            rs[0] = __funnelshift_r(o[0], o[1], 8) ^ cw[0];
+            rs[1] = __funnelshift_r(o[1], o[2], 8) ^ cw[1];
+            rs[2] = __funnelshift_r(o[2], o[3], 8) ^ cw[2];
+            const uint32_t w3 = (o[3] >> 8) ^ cw[3];
+            *reinterpret_cast<uint16_t*>(right_s + 12) = (uint16_t)w3;
+            right_s[14] = (uint8_t)(w3 >> 16);
+        }
+    } else {
+        if (right_s) right_s[15] = (uint8_t)(o[0] ^ (cw[3] >> 24));
+        if (right_t) *right_t = (uint8_t)(((o[0] >> 8) & 1u) ^ (t & (uint32_t)(qc.cw_tr >> level) & 1u));
+    }
+}
+
+constexpr uint32_t kCoopMaxLevel = 6;  // breadth-first levels with <= 64 nodes use coop_block
+
 // ---- tree role ------------------------------------------------------------------------------------
 __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan& ap, uint32_t lc) {
     const uint32_t tid = threadIdx.x, warp = tid >> 5;
@@ -156,7 +201,7 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
     uint8_t* bfs_t = g_smem2 + kOffBfsT;
     uint32_t* words = reinterpret_cast<uint32_t*>(g_smem2 + kOffWords);
     uint4* path_s = reinterpret_cast<uint4*>(g_smem2 + kOffPathS);
-    uint32_t* path_t = reinterpret_cast<uint32_t*>(g_smem2 + kOffPathT);
+    uint8_t* path_t = g_smem2 + kOffPathT;
 
     // contiguous block of tasks for this CTA
     const uint64_t k0 = (uint64_t)blockIdx.x * ap.task_count / gridDim.x;
@@ -165,43 +210,54 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
     for (uint64_t k = k0; k < k1; k++) {
         const uint32_t it = (uint32_t)(k - k0), buf = it & 1u;
         const uint64_t p = ap.task_first + k;  // node index at level Fc
-        // -- top walk: thread 0 re-expands from the common ancestor of the previous task's root --
-        if (tid == 0) {
+        // -- top walk: re-expand from the common ancestor with the previous task's root (3 threads) --
+        const uint32_t ck = warp & 3u, cj = (warp >> 2) * 32u + (tid & 31u);  // coop role: block ck of node cj
+        const bool coop_warp = ck < 3u && warp < 8u;
+        {
             uint32_t cp = 0;
             if (it == 0) {
-                path_s[0] = make_uint4(qc.s_init[0], qc.s_init[1], qc.s_init[2], qc.s_init[3]);
-                path_t[0] = qc.t_init;
+                if (tid == 0) {
+                    path_s[0] = make_uint4(qc.s_init[0], qc.s_init[1], qc.s_init[2], qc.s_init[3]);
+                    path_t[0] = (uint8_t)qc.t_init;
+                }
+                bar_sync(BAR_TREE, kTreeThreads);
             } else {
-                const uint64_t x = p ^ p_prev;
-                cp = Fc - (64u - (uint32_t)__clzll((long long)x));
+                cp = Fc - (64u - (uint32_t)__clzll((long long)(p ^ p_prev)));
             }
             for (uint32_t l = cp; l < Fc; l++) {
-                const uint4 sv = path_s[l];
-                const uint32_t s[4] = {sv.x, sv.y, sv.z, sv.w};
-                Children ch;
-                expand_node<1>(qc, s, path_t[l], l, lc, ch);
-                const uint32_t bit = (uint32_t)(p >> (Fc - 1 - l)) & 1u;
-                path_s[l + 1] = bit ? make_uint4(ch.sr[0], ch.sr[1], ch.sr[2], ch.sr[3])
-                                    : make_uint4(ch.sl[0], ch.sl[1], ch.sl[2], ch.sl[3]);
-                path_t[l + 1] = bit ? ch.tr : ch.tl;
+                if (coop_warp && cj == 0) {
+                    const uint32_t bit = (uint32_t)(p >> (Fc - 1 - l)) & 1u;
+                    uint8_t* ds = reinterpret_cast<uint8_t*>(&path_s[l + 1]);
+                    coop_block(qc, ck, path_s[l], path_t[l], l, lc, bit ? nullptr : ds, bit ? nullptr : &path_t[l + 1],
+                               bit ? ds : nullptr, bit ? &path_t[l + 1] : nullptr);
+                }
+                bar_sync(BAR_TREE, kTreeThreads);
             }
-            bfs_s[0] = path_s[Fc];
-            bfs_t[0] = (uint8_t)path_t[Fc];
+            if (tid == 0) {
+                bfs_s[0] = path_s[Fc];
+                bfs_t[0] = path_t[Fc];
+            }
         }
         p_prev = p;
         bar_sync(BAR_TREE, kTreeThreads);
         // -- B breadth-first levels: 2^B thread roots --
         for (uint32_t b = 0; b < B; b++) {
-            if (tid < (1u << b)) {
+            const uint32_t o = ((b + 1) & 1) * kTreeThreads;
+            if (b <= kCoopMaxLevel) {
+                if (coop_warp && cj < (1u << b)) {
+                    uint8_t* cs = reinterpret_cast<uint8_t*>(&bfs_s[o + 2 * cj]);
+                    coop_block(qc, ck, bfs_s[(b & 1) * kTreeThreads + cj], bfs_t[(b & 1) * kTreeThreads + cj], Fc + b, lc,
+                               cs, &bfs_t[o + 2 * cj], cs + 16, &bfs_t[o + 2 * cj + 1]);
+                }
+            } else if (tid < (1u << b)) {
                 const uint4 sv = bfs_s[(b & 1) * kTreeThreads + tid];
                 const uint32_t s[4] = {sv.x, sv.y, sv.z, sv.w};
                 Children ch;
                 expand_node<1>(qc, s, bfs_t[(b & 1) * kTreeThreads + tid], Fc + b, lc, ch);
-                const uint32_t o = ((b + 1) & 1) * kTreeThreads + 2 * tid;
-                bfs_s[o] = make_uint4(ch.sl[0], ch.sl[1], ch.sl[2], ch.sl[3]);
-                bfs_s[o + 1] = make_uint4(ch.sr[0], ch.sr[1], ch.sr[2], ch.sr[3]);
-                bfs_t[o] = (uint8_t)ch.tl;
-                bfs_t[o + 1] = (uint8_t)ch.tr;
+                bfs_s[o + 2 * tid] = make_uint4(ch.sl[0], ch.sl[1], ch.sl[2], ch.sl[3]);
+                bfs_s[o + 2 * tid + 1] = make_uint4(ch.sr[0], ch.sr[1], ch.sr[2], ch.sr[3]);
+                bfs_t[o + 2 * tid] = (uint8_t)ch.tl;
+                bfs_t[o + 2 * tid + 1] = (uint8_t)ch.tr;
             }
             bar_sync(BAR_TREE, kTreeThreads);
         }
