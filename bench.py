@@ -278,6 +278,13 @@ def gpu_arm(args):
         peak = float(peaks.get("hbm_gbs", 6650.0))
         shard_bytes = (r1 - r0) * S
         achieved = shard_bytes / (k_avg_ms * 1e-3) / 1e9
+        traffic = None
+        try:
+            tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["answer_kernel"]
+            if world == tr["n_gpus"] and tr["workload"] in workload_name():
+                traffic = tr["dram_bytes_read"] + tr["dram_bytes_write"]
+        except Exception:
+            pass
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
@@ -292,7 +299,7 @@ def gpu_arm(args):
                     "api": "pir_answer (C ABI, host key in / host answer out, stream sync per query)"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": "fused_kernel<1,false>", "kernel_ms": k_avg_ms,
+                         "traffic": traffic, "kernel": "answer_kernel", "kernel_ms": k_avg_ms,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650",
                          "algorithmic_bytes_per_launch": shard_bytes,
                          "aes_blocks_per_s": 3.0 * (r1 - r0) / (k_avg_ms * 1e-3)},
