@@ -3,8 +3,8 @@
 
 A step = one query answered over the whole database (one pass of the hot path).  Workload at every N:
 BASELINE.json configs[2], 2^24 rows x 256-byte slots (4 GiB), single query; at N > 1 the SAME
-database is row-sharded over the N GPUs (strong scaling) and the per-GPU partial answers are
-XOR-combined every step.
+database is row-sharded over the N GPUs (strong scaling) and every shard's kernel XORs its partial
+answer straight into a ring slot on rank 0's GPU (CUDA IPC mapping over NVLink; no NCCL in the data path).
 
   value     GB/s of database scanned per query with the database resident in HBM (device-timed)
   e2e       the same through pir_answer() with HOST buffers: key in, answer out, sync per query
@@ -174,20 +174,20 @@ def gpu_arm(args):
 
     stream = torch.cuda.Stream()
     d_out = torch.zeros(S, dtype=torch.uint8, device="cuda")
-    gathered = torch.zeros(world * S, dtype=torch.uint8, device="cuda") if world > 1 else None
     sp = C.c_void_p(stream.cuda_stream)
+    comb = None
+    if world > 1:
+        # one ring slot per step of either timed region plus two for the acceptance check; the slots live on
+        # rank 0's GPU and every rank's kernel XORs its partial straight into them (CUDA IPC mapping, NVLink)
+        from pir_b200 import sharding
+        comb = sharding.open_combine_over_group(dist, local, 2 * total + 2, S, owner=0)
 
-    def step_device(i):
-        """one query, database resident, answer left on the device (combined on every rank)"""
-        _capi.check(L.pir_answer_batch_device(h, C.byref(qs[2 * i]), 1, C.c_void_p(d_out.data_ptr()), sp))
+    def step_device(i, slot=None):
+        """one query, database resident; N > 1: every rank's kernel accumulates into ring slot `slot` on rank 0"""
         if world > 1:
-            with torch.cuda.stream(stream):
-                dist.all_gather_into_tensor(gathered, d_out)
-                comb = gathered.view(world, S)[0]
-                for g in range(1, world):
-                    comb = comb ^ gathered.view(world, S)[g]
-            return comb
-        return d_out
+            comb.accumulate(h, qs[2 * i], i if slot is None else slot, sp)
+        else:
+            _capi.check(L.pir_answer_batch_device(h, C.byref(qs[2 * i]), 1, C.c_void_p(d_out.data_ptr()), sp))
 
     def barrier():
         torch.cuda.synchronize()
@@ -198,20 +198,29 @@ def gpu_arm(args):
     # ---- acceptance check (outside the timed region): both shares recover the queried slot ----
     i = total
     host = np.zeros(S, dtype=np.uint8)
-    acc = torch.zeros(S, dtype=torch.uint8, device="cuda")
-    for share in (0, 1):
-        _capi.check(L.pir_answer_batch_device(h, C.byref(qs[2 * i + share]), 1, C.c_void_p(d_out.data_ptr()), sp))
-        stream.synchronize()
-        acc ^= d_out
-    if world > 1:
-        allp = torch.zeros(world * S, dtype=torch.uint8, device="cuda")
-        dist.all_gather_into_tensor(allp, acc)
-        acc = allp.view(world, S)[0].clone()
-        for g in range(1, world):
-            acc ^= allp.view(world, S)[g]
-    if r0 <= idxs[i] < r1:
+    if world == 1:
+        acc = torch.zeros(S, dtype=torch.uint8, device="cuda")
+        for share in (0, 1):
+            _capi.check(L.pir_answer_batch_device(h, C.byref(qs[2 * i + share]), 1, C.c_void_p(d_out.data_ptr()), sp))
+            stream.synchronize()
+            acc ^= d_out
+        recovered = acc.cpu().numpy()
+    else:
+        for share in (0, 1):
+            comb.accumulate(h, qs[2 * i + share], 2 * total + share, sp)
+        barrier()
+        recovered = None
+        if rank == 0:
+            recovered = comb.wait_read(2 * total, world, S) ^ comb.wait_read(2 * total + 1, world, S)
+    box = [None]
+    owner_rank = next(r for r in range(world) if r * n // world <= idxs[i] < (r + 1) * n // world)
+    if rank == owner_rank:
         _capi.check(L.pir_db_download(h, idxs[i], host.ctypes.data_as(C.c_void_p), 1))
-        if not np.array_equal(acc.cpu().numpy(), host) and not os.environ.get("PIRB_BENCH_NOCHECK"):
+        box[0] = host.tobytes()
+    if world > 1:
+        dist.broadcast_object_list(box, src=owner_rank)
+    if rank == 0 and not os.environ.get("PIRB_BENCH_NOCHECK"):
+        if not np.array_equal(recovered, np.frombuffer(box[0], dtype=np.uint8)):
             raise SystemExit("bench.py: recovered slot differs from the database slot — refusing to time a wrong path")
 
     # ---- warm-up ----
@@ -238,22 +247,23 @@ def gpu_arm(args):
     _capi.check(L.pir_db_get_kernel_timing(h, C.byref(kms), C.byref(kcount)))
     _capi.check(L.pir_db_set_kernel_timing(h, 0))
 
-    # ---- end-to-end timed region: host buffers in, host answer out, every step ----
+    # ---- end-to-end timed region: host key in, host answer out, every step ----
     out_host = np.zeros(S, dtype=np.uint8)
-    comb_host = np.zeros(S, dtype=np.uint8)
-    for i in range(min(3, args.warmup)):
-        _capi.check(L.pir_answer(h, C.byref(qs[2 * i]), out_host.ctypes.data_as(C.c_void_p), S))
+    e2e_ok = True
+    if world == 1:
+        for i in range(min(3, args.warmup)):
+            _capi.check(L.pir_answer(h, C.byref(qs[2 * i]), out_host.ctypes.data_as(C.c_void_p), S))
     barrier()
     t0 = time.perf_counter()
     for i in range(args.warmup, total):
-        _capi.check(L.pir_answer(h, C.byref(qs[2 * i]), out_host.ctypes.data_as(C.c_void_p), S))
-        if world > 1:
-            parts = [None] * world if rank == 0 else None
-            dist.gather_object(out_host.tobytes(), parts, dst=0)  # host reduction of N partial answers
+        if world == 1:
+            _capi.check(L.pir_answer(h, C.byref(qs[2 * i]), out_host.ctypes.data_as(C.c_void_p), S))
+        else:
+            # every rank: host key -> its shard's kernel -> XOR into ring slot on rank 0;
+            # rank 0: device-side wait for all N arrivals, then the combined answer comes back to the host
+            comb.accumulate(h, qs[2 * i], total + i, None)
             if rank == 0:
-                comb_host[:] = 0
-                for p in parts:
-                    L.pir_xor_combine(comb_host.ctypes.data_as(C.c_void_p), p, S)
+                out_host = comb.wait_read(total + i, world, S)
     barrier()
     e2e_ms = (time.perf_counter() - t0) * 1e3
     clocks = sampler.stop() if rank == 0 else None
@@ -291,12 +301,14 @@ def gpu_arm(args):
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": workload_name(), "sharding": "rows/%d" % world,
                        "l2": "per-GPU shard (%d MiB) exceeds the 126 MB L2; every step scans all of it" % (shard_bytes >> 20),
-                       "combine": "none" if world == 1 else "all_gather of %d-byte partials + XOR" % S,
+                       "combine": "none" if world == 1 else "every shard's kernel XORs its %d-byte partial into rank 0's ring slot "
+                                  "(red.global.xor over a CUDA IPC mapping / NVLink); no NCCL in the data path" % S,
                        "queries": "distinct seeded key per step, share 0"},
             "queries_per_s": 1e3 / ms_step,
             "e2e": {"value": db_bytes / (e2e_step * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": e2e_step,
                     "h2d_bytes_per_step": C.sizeof(_capi.PirQuery), "d2h_bytes_per_step": S,
-                    "api": "pir_answer (C ABI, host key in / host answer out, stream sync per query)"},
+                    "api": "pir_answer (C ABI, host key in / host answer out, stream sync per query)" if world == 1 else
+                           "pir_answer_accumulate_device on every rank + pir_combine_wait_read on rank 0 (host key in, combined host answer out)"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "kernel": "answer_kernel", "kernel_ms": k_avg_ms,
@@ -309,6 +321,13 @@ def gpu_arm(args):
             gbs, ms, cores, sample = cpu_reference_run(3, 1)
             line["cpu_baseline"] = {"value": gbs, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
         print(json.dumps(line), flush=True)
+    if comb is not None:
+        barrier()
+        if rank != 0:
+            comb.close()   # peers unmap before the owner frees
+        dist.barrier()
+        if rank == 0:
+            comb.close()
     L.pir_db_destroy(h)
     if world > 1:
         dist.destroy_process_group()

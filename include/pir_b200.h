@@ -129,6 +129,58 @@ int pir_db_rows(const pir_db* db, uint32_t group_size, uint64_t* first_row, uint
 int pir_answer_batch_device(pir_db* db, const pir_query* qs, uint32_t n_queries, void* d_out,
                             void* stream);
 
+/* ---- multi-GPU: one PIR server row-sharded over the GPUs of a box ---------------- */
+/*
+ * The answer is an XOR over rows (db.go:91-104), so GPU g holds rows [g*H/G, (g+1)*H/G) and every
+ * shard's kernel XORs its partial answer straight into ONE combine slot with red.global.xor — on the
+ * owner GPU that is local memory, on the others it is the owner's memory mapped over NVLink (peer
+ * access or CUDA IPC).  No NCCL (it has no XOR reduction), no extra combine pass.
+ *
+ * pir_server: ONE process drives all shards (what a Go server does: one cgo call per query).
+ */
+typedef struct pir_server pir_server; /* opaque */
+/* devices[i] is the CUDA device of shard i (a device may appear more than once: several shards on one
+ * GPU).  Shard boundaries are multiples of shard_align slots (pass the largest group size the
+ * database will be queried with, or 1). */
+int pir_server_create(const int* devices, int n_devices, uint64_t db_size, uint32_t slot_bytes,
+                      uint32_t shard_align, pir_server** out);
+int pir_server_destroy(pir_server* s);
+int pir_server_num_shards(const pir_server* s);
+/* Borrow shard i's handle (owned by the server) for upload / keywords / per-shard calls. */
+int pir_server_shard(pir_server* s, int i, pir_db** db);
+int pir_server_upload(pir_server* s, uint64_t slot_index, const void* host_slots, uint64_t n_slots);
+int pir_server_fill_synthetic(pir_server* s, uint64_t seed);
+/* PrivateSecretSharedQuery (db.go:68-72) over all shards: out gets group_size*slot_bytes bytes. */
+int pir_server_answer(pir_server* s, const pir_query* q, void* out, size_t out_len);
+int pir_server_answer_batch(pir_server* s, const pir_query* qs, uint32_t n_queries, void* out, size_t out_len);
+
+/*
+ * pir_combine: the same combine for ONE PROCESS PER GPU (torchrun-style launch).  The owner rank
+ * creates a ring of n_slots answer slots of slot_stride bytes plus one arrival counter per slot and
+ * exports a CUDA IPC handle; every other rank opens it.  Per query every rank calls
+ * pir_answer_accumulate_device on the same slot; the owner then waits for `world` arrivals and reads
+ * the combined answer.  A slot must be re-zeroed by the owner (pir_combine_reset) before it is reused,
+ * and no rank may accumulate into it before that reset is complete (the caller's barrier).
+ */
+#define PIR_IPC_HANDLE_BYTES 64
+typedef struct pir_combine pir_combine; /* opaque */
+int pir_combine_create(int device, uint32_t n_slots, size_t slot_stride, pir_combine** out);
+int pir_combine_export(pir_combine* c, uint8_t handle[PIR_IPC_HANDLE_BYTES]);
+int pir_combine_open(int device, const uint8_t handle[PIR_IPC_HANDLE_BYTES], uint32_t n_slots,
+                     size_t slot_stride, pir_combine** out);
+int pir_combine_destroy(pir_combine* c);
+/* Owner only: zero slots [first, first+count) and their arrival counters; blocks until done. */
+int pir_combine_reset(pir_combine* c, uint32_t first, uint32_t count);
+/* Any rank: XOR this shard's partial answer of q into slot `slot` (pitched layout, like
+ * pir_answer_batch_device) and signal arrival.  Only enqueues work on `stream` (NULL = the handle's). */
+int pir_answer_accumulate_device(pir_db* db, const pir_query* q, pir_combine* c, uint32_t slot, void* stream);
+/* Owner only: wait (on the device, bounded by timeout_ms) until `expected` ranks have arrived at the
+ * slot, then copy its first out_len bytes to host memory.  PIR_ERR_CUDA on timeout. */
+int pir_combine_wait_read(pir_combine* c, uint32_t slot, uint32_t expected, void* out, size_t out_len,
+                          uint32_t timeout_ms);
+/* Device address of a slot in this process (for device-resident consumers / tests). */
+void* pir_combine_slot_ptr(pir_combine* c, uint32_t slot);
+
 /* ---- dpf package surface ---------------------------------------------------------------------- */
 /* (*Dpf).Evaluate2P (dpf/server.go:55-101) on n points: out[i] = Evaluate2P(share_number, key, xs[i])
  * as wrapping int64.  Uses q->num_bits levels; runs on `device`. */

@@ -31,7 +31,12 @@ EXPORTS = [
     "pir_answer_batch_device", "pir_dpf_eval_points", "pir_xor_combine", "pir_num_bits_for",
     "pir_kernel_launch_count", "pir_client_gen_two_server",
     "pir_db_set_kernel_timing", "pir_db_get_kernel_timing",
+    "pir_server_create", "pir_server_destroy", "pir_server_num_shards", "pir_server_shard",
+    "pir_server_upload", "pir_server_fill_synthetic", "pir_server_answer", "pir_server_answer_batch",
+    "pir_combine_create", "pir_combine_export", "pir_combine_open", "pir_combine_destroy",
+    "pir_combine_reset", "pir_answer_accumulate_device", "pir_combine_wait_read", "pir_combine_slot_ptr",
 ]
+PIR_IPC_HANDLE_BYTES = 64
 
 
 class PirQuery(C.Structure):
@@ -121,6 +126,23 @@ def lib():
     L.pir_client_gen_two_server.argtypes = [C.c_uint32, C.c_uint64, C.c_uint64, u8p, qp, qp]
     L.pir_db_set_kernel_timing.argtypes = [vp, C.c_int]
     L.pir_db_get_kernel_timing.argtypes = [vp, C.POINTER(C.c_double), u64p]
+    L.pir_server_create.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint64, C.c_uint32, C.c_uint32, C.POINTER(vp)]
+    L.pir_server_destroy.argtypes = [vp]
+    L.pir_server_num_shards.argtypes = [vp]
+    L.pir_server_shard.argtypes = [vp, C.c_int, C.POINTER(vp)]
+    L.pir_server_upload.argtypes = [vp, C.c_uint64, vp, C.c_uint64]
+    L.pir_server_fill_synthetic.argtypes = [vp, C.c_uint64]
+    L.pir_server_answer.argtypes = [vp, qp, vp, C.c_size_t]
+    L.pir_server_answer_batch.argtypes = [vp, qp, C.c_uint32, vp, C.c_size_t]
+    L.pir_combine_create.argtypes = [C.c_int, C.c_uint32, C.c_size_t, C.POINTER(vp)]
+    L.pir_combine_export.argtypes = [vp, u8p]
+    L.pir_combine_open.argtypes = [C.c_int, u8p, C.c_uint32, C.c_size_t, C.POINTER(vp)]
+    L.pir_combine_destroy.argtypes = [vp]
+    L.pir_combine_reset.argtypes = [vp, C.c_uint32, C.c_uint32]
+    L.pir_answer_accumulate_device.argtypes = [vp, qp, vp, C.c_uint32, vp]
+    L.pir_combine_wait_read.argtypes = [vp, C.c_uint32, C.c_uint32, vp, C.c_size_t, C.c_uint32]
+    L.pir_combine_slot_ptr.argtypes = [vp, C.c_uint32]
+    L.pir_combine_slot_ptr.restype = vp
     L.pir_debug_round_keys.argtypes = [u8p, C.POINTER(C.c_uint32)]
     L.pir_debug_t0.argtypes = [C.POINTER(C.c_uint32)]
     if L.pir_abi_version() != 1:

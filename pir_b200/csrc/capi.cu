@@ -108,6 +108,7 @@ struct DeviceCtx {
     uint32_t* d_t0 = nullptr;
     uint32_t smem_base = 0;
     int num_sms = 0;
+    int clock_khz = 0;
 };
 std::mutex g_dev_mu;
 DeviceCtx g_dev[64];
@@ -126,6 +127,8 @@ int device_ctx(int device, DeviceCtx** out) {
             return fail(PIR_ERR_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", device,
                         prop.major, prop.minor);
         c.num_sms = prop.multiProcessorCount;
+        // queried once: cudaDeviceGetAttribute(cudaDevAttrClockRate) takes milliseconds on this driver
+        CU(cudaDeviceGetAttribute(&c.clock_khz, cudaDevAttrClockRate, device));
         CU(cudaMalloc(&c.d_t0, 1024));
         CU(cudaMemcpy(c.d_t0, aes_host().t0, 1024, cudaMemcpyHostToDevice));
         CU(configure_kernels());
@@ -496,8 +499,11 @@ int query_geom(const pir_db* db, const pir_query* q, QueryGeom* g) {
 }
 
 // Enqueue one query's work on `st`; d_out receives the pitched answer (row_bytes bytes).
-int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* d_out, cudaStream_t st) {
-    CU(cudaMemsetAsync(d_out, 0, g.row_bytes, st));
+int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* d_out, cudaStream_t st,
+                   bool zero_first = true) {
+    // every kernel below XOR-accumulates into d_out (atomics), so a caller that combines several shards
+    // into one buffer passes zero_first = false and zeroes it once itself
+    if (zero_first) CU(cudaMemsetAsync(d_out, 0, g.row_bytes, st));
     if (g.n_rows == 0) return PIR_OK;
     QueryConst qc;
     int rc = build_query_const(q, g.nb, &qc);
@@ -871,4 +877,375 @@ extern "C" void pir_debug_plan(uint32_t nb, uint64_t first_row, uint64_t n_rows,
                                uint32_t* B, uint32_t* Fc, uint64_t* task_first, uint64_t* task_count) {
     Plan p = make_plan(nb, first_row, n_rows, num_sms);
     *D = p.D; *B = p.B; *Fc = p.Fc; *task_first = p.task_first; *task_count = p.task_count;
+}
+
+// ---- multi-GPU combine ------------------------------------------------------------
+// Layout of a combine buffer on the owner GPU: [n_slots x slot_stride answer bytes][n_slots x u32 arrivals]
+// [u32 timeout flag].  slot_stride is a multiple of 16.
+struct pir_combine {
+    int device = 0;          // device of THIS process that uses the mapping
+    bool owner = false;
+    uint32_t n_slots = 0;
+    size_t stride = 0;
+    uint8_t* base = nullptr;  // device pointer valid in this process
+    cudaStream_t stream = nullptr;  // owner: reset / wait / read
+    uint8_t* h_buf = nullptr;       // owner: pinned staging of one slot + the timeout flag
+    int clock_khz = 0;
+    std::mutex mu;
+    uint32_t* arrivals(uint32_t slot) const { return (uint32_t*)(base + (size_t)n_slots * stride) + slot; }
+    uint32_t* timeout_flag() const { return (uint32_t*)(base + (size_t)n_slots * stride) + n_slots; }
+    size_t total_bytes() const { return (size_t)n_slots * stride + ((size_t)n_slots + 1) * 4; }
+};
+
+static int combine_args(uint32_t n_slots, size_t slot_stride) {
+    if (n_slots == 0 || slot_stride == 0 || (slot_stride & 15))
+        return fail(PIR_ERR_BAD_ARG, "combine needs n_slots >= 1 and a slot_stride that is a non-zero multiple of 16");
+    return PIR_OK;
+}
+
+extern "C" int pir_combine_create(int device, uint32_t n_slots, size_t slot_stride, pir_combine** out) {
+    if (!out) return fail(PIR_ERR_BAD_ARG, "out is null");
+    *out = nullptr;
+    int rc = combine_args(n_slots, slot_stride);
+    if (rc) return rc;
+    DeviceCtx* ctx = nullptr;
+    if ((rc = device_ctx(device, &ctx))) return rc;
+    DeviceGuard g(device);
+    pir_combine* c = new (std::nothrow) pir_combine();
+    if (!c) return fail(PIR_ERR_OOM, "host allocation failed");
+    c->device = device;
+    c->owner = true;
+    c->n_slots = n_slots;
+    c->stride = slot_stride;
+    cudaError_t e = cudaMalloc(&c->base, c->total_bytes());  // plain cudaMalloc: exportable with CUDA IPC
+    if (e == cudaSuccess) e = cudaMemset(c->base, 0, c->total_bytes());
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMallocHost(&c->h_buf, slot_stride + 16);
+    c->clock_khz = ctx->clock_khz;
+    if (e != cudaSuccess) {
+        int code = e == cudaErrorMemoryAllocation ? PIR_ERR_OOM : PIR_ERR_CUDA;
+        fail(code, "pir_combine_create: %s", cudaGetErrorString(e));
+        cudaGetLastError();
+        pir_combine_destroy(c);
+        return code;
+    }
+    *out = c;
+    return PIR_OK;
+}
+
+extern "C" int pir_combine_export(pir_combine* c, uint8_t handle[PIR_IPC_HANDLE_BYTES]) {
+    if (!c || !handle) return fail(PIR_ERR_BAD_ARG, "null argument");
+    if (!c->owner) return fail(PIR_ERR_BAD_ARG, "only the owner can export a combine buffer");
+    static_assert(sizeof(cudaIpcMemHandle_t) == PIR_IPC_HANDLE_BYTES, "CUDA IPC handle size");
+    DeviceGuard g(c->device);
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, c->base));
+    memcpy(handle, &h, sizeof h);
+    return PIR_OK;
+}
+
+extern "C" int pir_combine_open(int device, const uint8_t handle[PIR_IPC_HANDLE_BYTES], uint32_t n_slots,
+                                size_t slot_stride, pir_combine** out) {
+    if (!out || !handle) return fail(PIR_ERR_BAD_ARG, "null argument");
+    *out = nullptr;
+    int rc = combine_args(n_slots, slot_stride);
+    if (rc) return rc;
+    DeviceCtx* ctx = nullptr;
+    if ((rc = device_ctx(device, &ctx))) return rc;
+    DeviceGuard g(device);
+    pir_combine* c = new (std::nothrow) pir_combine();
+    if (!c) return fail(PIR_ERR_OOM, "host allocation failed");
+    c->device = device;
+    c->owner = false;
+    c->n_slots = n_slots;
+    c->stride = slot_stride;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof h);
+    void* p = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+        delete c;
+        cudaGetLastError();
+        return fail(PIR_ERR_CUDA, "cudaIpcOpenMemHandle: %s", cudaGetErrorString(e));
+    }
+    c->base = (uint8_t*)p;
+    *out = c;
+    return PIR_OK;
+}
+
+extern "C" int pir_combine_destroy(pir_combine* c) {
+    if (!c) return PIR_OK;
+    DeviceGuard g(c->device);
+    if (c->owner) {
+        if (c->stream) {
+            cudaStreamSynchronize(c->stream);
+            cudaStreamDestroy(c->stream);
+        }
+        if (c->h_buf) cudaFreeHost(c->h_buf);
+        if (c->base) cudaFree(c->base);
+    } else if (c->base) {
+        cudaDeviceSynchronize();
+        cudaIpcCloseMemHandle(c->base);
+    }
+    delete c;
+    return PIR_OK;
+}
+
+extern "C" int pir_combine_reset(pir_combine* c, uint32_t first, uint32_t count) {
+    if (!c) return fail(PIR_ERR_BAD_ARG, "null handle");
+    if (!c->owner) return fail(PIR_ERR_BAD_ARG, "only the owner resets combine slots");
+    if (first > c->n_slots || count > c->n_slots - first) return fail(PIR_ERR_BAD_ARG, "slot range out of bounds");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->device);
+    CU(cudaMemsetAsync(c->base + (size_t)first * c->stride, 0, (size_t)count * c->stride, c->stream));
+    CU(cudaMemsetAsync(c->arrivals(first), 0, (size_t)count * 4, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return PIR_OK;
+}
+
+extern "C" void* pir_combine_slot_ptr(pir_combine* c, uint32_t slot) {
+    if (!c || slot >= c->n_slots) return nullptr;
+    return c->base + (size_t)slot * c->stride;
+}
+
+extern "C" int pir_answer_accumulate_device(pir_db* db, const pir_query* q, pir_combine* c, uint32_t slot,
+                                            void* stream) {
+    if (!db || !q || !c) return fail(PIR_ERR_BAD_ARG, "null argument");
+    if (slot >= c->n_slots) return fail(PIR_ERR_BAD_ARG, "slot %u out of range (%u slots)", slot, c->n_slots);
+    if (c->device != db->device)
+        return fail(PIR_ERR_BAD_ARG, "combine buffer is mapped on device %d, the shard lives on device %d", c->device,
+                    db->device);
+    std::lock_guard<std::mutex> lk(db->mu);
+    DeviceGuard g(db->device);
+    cudaStream_t st = stream ? (cudaStream_t)stream : db->stream;
+    QueryGeom geom;
+    int rc = query_geom(db, q, &geom);
+    if (rc) return rc;
+    if (geom.row_bytes > c->stride) return fail(PIR_ERR_BAD_ARG, "answer of %llu bytes exceeds the slot stride %zu",
+                                                (unsigned long long)geom.row_bytes, c->stride);
+    if ((rc = enqueue_answer(db, q, geom, c->base + (size_t)slot * c->stride, st, /*zero_first=*/false))) return rc;
+    CU(launch_signal_arrival(c->arrivals(slot), st));
+    return PIR_OK;
+}
+
+extern "C" int pir_combine_wait_read(pir_combine* c, uint32_t slot, uint32_t expected, void* out, size_t out_len,
+                                     uint32_t timeout_ms) {
+    if (!c || !out) return fail(PIR_ERR_BAD_ARG, "null argument");
+    if (!c->owner) return fail(PIR_ERR_BAD_ARG, "only the owner reads combine slots");
+    if (slot >= c->n_slots || out_len > c->stride) return fail(PIR_ERR_BAD_ARG, "slot or length out of range");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->device);
+    const uint64_t cycles = (uint64_t)(c->clock_khz > 0 ? c->clock_khz : 1000000) * (timeout_ms ? timeout_ms : 1);
+    CU(launch_wait_arrivals(c->arrivals(slot), expected, cycles, c->timeout_flag(), c->stream));
+    CU(cudaMemcpyAsync(c->h_buf, c->base + (size_t)slot * c->stride, out_len, cudaMemcpyDeviceToHost, c->stream));
+    uint32_t* h_flag = (uint32_t*)(c->h_buf + c->stride);
+    CU(cudaMemcpyAsync(h_flag, c->timeout_flag(), 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (*h_flag) {
+        cudaMemsetAsync(c->timeout_flag(), 0, 4, c->stream);
+        cudaStreamSynchronize(c->stream);
+        return fail(PIR_ERR_CUDA, "timed out after %u ms waiting for %u shard arrivals at combine slot %u", timeout_ms,
+                    expected, slot);
+    }
+    memcpy(out, c->h_buf, out_len);
+    return PIR_OK;
+}
+
+// ---- pir_server: one process, all shards -----------------------------------------------------------
+struct pir_server {
+    std::vector<pir_db*> shards;
+    std::vector<cudaEvent_t> done;   // per shard: its partial has been accumulated
+    cudaEvent_t zeroed = nullptr;    // owner stream: the accumulator has been cleared
+    int owner_device = 0;
+    uint64_t db_size = 0;
+    uint32_t slot_bytes = 0, pitch = 0;
+    uint8_t* d_acc = nullptr;        // on the owner device; peers reach it over NVLink (peer access)
+    uint64_t acc_cap = 0;
+    uint8_t* h_acc = nullptr;        // pinned
+    cudaStream_t stream = nullptr;   // owner stream
+    std::mutex mu;
+};
+
+namespace {
+int server_ensure_acc(pir_server* s, uint64_t n) {
+    if (n <= s->acc_cap) return PIR_OK;
+    DeviceGuard g(s->owner_device);
+    if (s->d_acc) cudaFree(s->d_acc);
+    if (s->h_acc) cudaFreeHost(s->h_acc);
+    s->d_acc = nullptr;
+    s->h_acc = nullptr;
+    s->acc_cap = 0;
+    CU(cudaMalloc(&s->d_acc, n));
+    CU(cudaMallocHost(&s->h_acc, n));
+    s->acc_cap = n;
+    return PIR_OK;
+}
+}  // namespace
+
+extern "C" int pir_server_create(const int* devices, int n_devices, uint64_t db_size, uint32_t slot_bytes,
+                                 uint32_t shard_align, pir_server** out) {
+    if (!out) return fail(PIR_ERR_BAD_ARG, "out is null");
+    *out = nullptr;
+    if (!devices || n_devices <= 0) return fail(PIR_ERR_BAD_ARG, "need at least one device");
+    if (db_size == 0 || slot_bytes == 0) return fail(PIR_ERR_BAD_ARG, "db_size and slot_bytes must be non-zero");
+    if (shard_align == 0) shard_align = 1;
+    pir_server* s = new (std::nothrow) pir_server();
+    if (!s) return fail(PIR_ERR_OOM, "host allocation failed");
+    s->db_size = db_size;
+    s->slot_bytes = slot_bytes;
+    s->pitch = (slot_bytes + 15u) & ~15u;
+    s->owner_device = devices[0];
+    const uint64_t units = db_size / shard_align;  // whole alignment units; the ragged tail goes to the last shard
+    int rc = PIR_OK;
+    for (int i = 0; i < n_devices && rc == PIR_OK; i++) {
+        const uint64_t b = units * (uint64_t)i / (uint64_t)n_devices * shard_align;
+        const uint64_t e = i == n_devices - 1 ? db_size : units * (uint64_t)(i + 1) / (uint64_t)n_devices * shard_align;
+        pir_db* db = nullptr;
+        rc = pir_db_create(devices[i], db_size, slot_bytes, b, e - b, &db);
+        if (rc == PIR_OK) s->shards.push_back(db);
+    }
+    // peer access: every shard's device must be able to store into the owner's memory
+    for (size_t i = 0; i < s->shards.size() && rc == PIR_OK; i++) {
+        const int dev = s->shards[i]->device;
+        if (dev == s->owner_device) continue;
+        int can = 0;
+        cudaError_t e = cudaDeviceCanAccessPeer(&can, dev, s->owner_device);
+        if (e != cudaSuccess || !can) {
+            rc = fail(PIR_ERR_CUDA, "device %d cannot access device %d as a peer (NVLink/P2P needed for the combine)", dev,
+                      s->owner_device);
+            break;
+        }
+        DeviceGuard g(dev);
+        e = cudaDeviceEnablePeerAccess(s->owner_device, 0);
+        if (e == cudaErrorPeerAccessAlreadyEnabled) {
+            cudaGetLastError();
+            e = cudaSuccess;
+        }
+        if (e != cudaSuccess) rc = fail(PIR_ERR_CUDA, "cudaDeviceEnablePeerAccess(%d -> %d): %s", dev, s->owner_device,
+                                        cudaGetErrorString(e));
+    }
+    if (rc == PIR_OK) {
+        DeviceGuard g(s->owner_device);
+        cudaError_t e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&s->zeroed, cudaEventDisableTiming);
+        if (e != cudaSuccess) rc = fail(PIR_ERR_CUDA, "pir_server_create: %s", cudaGetErrorString(e));
+    }
+    for (size_t i = 0; i < s->shards.size() && rc == PIR_OK; i++) {
+        DeviceGuard g(s->shards[i]->device);
+        cudaEvent_t ev = nullptr;
+        cudaError_t e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+        if (e != cudaSuccess) rc = fail(PIR_ERR_CUDA, "pir_server_create: %s", cudaGetErrorString(e));
+        else s->done.push_back(ev);
+    }
+    if (rc != PIR_OK) {
+        char keep[sizeof tl_err];
+        memcpy(keep, tl_err, sizeof keep);
+        pir_server_destroy(s);
+        memcpy(tl_err, keep, sizeof keep);
+        return rc;
+    }
+    *out = s;
+    return PIR_OK;
+}
+
+extern "C" int pir_server_destroy(pir_server* s) {
+    if (!s) return PIR_OK;
+    for (size_t i = 0; i < s->done.size(); i++) {
+        DeviceGuard g(s->shards[i]->device);
+        cudaEventDestroy(s->done[i]);
+    }
+    for (pir_db* db : s->shards) pir_db_destroy(db);
+    {
+        DeviceGuard g(s->owner_device);
+        if (s->stream) {
+            cudaStreamSynchronize(s->stream);
+            cudaStreamDestroy(s->stream);
+        }
+        if (s->zeroed) cudaEventDestroy(s->zeroed);
+        if (s->d_acc) cudaFree(s->d_acc);
+        if (s->h_acc) cudaFreeHost(s->h_acc);
+    }
+    delete s;
+    return PIR_OK;
+}
+
+extern "C" int pir_server_num_shards(const pir_server* s) { return s ? (int)s->shards.size() : 0; }
+
+extern "C" int pir_server_shard(pir_server* s, int i, pir_db** db) {
+    if (!s || !db) return fail(PIR_ERR_BAD_ARG, "null argument");
+    if (i < 0 || (size_t)i >= s->shards.size()) return fail(PIR_ERR_BAD_ARG, "shard %d out of range", i);
+    *db = s->shards[(size_t)i];
+    return PIR_OK;
+}
+
+extern "C" int pir_server_upload(pir_server* s, uint64_t slot_index, const void* host_slots, uint64_t n_slots) {
+    if (!s || (!host_slots && n_slots)) return fail(PIR_ERR_BAD_ARG, "null argument");
+    if (slot_index > s->db_size || n_slots > s->db_size - slot_index)
+        return fail(PIR_ERR_BAD_ARG, "slots [%llu, +%llu) exceed db_size", (unsigned long long)slot_index,
+                    (unsigned long long)n_slots);
+    for (pir_db* db : s->shards) {
+        const uint64_t b = slot_index > db->slot_begin ? slot_index : db->slot_begin;
+        const uint64_t e0 = slot_index + n_slots, e1 = db->slot_begin + db->slot_count;
+        const uint64_t e = e0 < e1 ? e0 : e1;
+        if (b >= e) continue;
+        int rc = pir_db_upload(db, b, (const uint8_t*)host_slots + (b - slot_index) * (uint64_t)s->slot_bytes, e - b);
+        if (rc) return rc;
+    }
+    return PIR_OK;
+}
+
+extern "C" int pir_server_fill_synthetic(pir_server* s, uint64_t seed) {
+    if (!s) return fail(PIR_ERR_BAD_ARG, "null handle");
+    for (pir_db* db : s->shards) {
+        int rc = pir_db_fill_synthetic(db, seed);
+        if (rc) return rc;
+    }
+    return PIR_OK;
+}
+
+extern "C" int pir_server_answer_batch(pir_server* s, const pir_query* qs, uint32_t n_queries, void* out,
+                                       size_t out_len) {
+    if (!s || !qs || !out || n_queries == 0) return fail(PIR_ERR_BAD_ARG, "null or empty argument");
+    std::lock_guard<std::mutex> lk(s->mu);
+    const uint32_t W = qs[0].group_size;
+    if (W == 0) return fail(PIR_ERR_BAD_ARG, "group_size must be >= 1");
+    const uint64_t row_bytes = (uint64_t)W * s->pitch;
+    const size_t ans = (size_t)W * s->slot_bytes;
+    if (out_len < ans * n_queries) return fail(PIR_ERR_BAD_ARG, "out_len %zu < %zu", out_len, ans * n_queries);
+    int rc = server_ensure_acc(s, row_bytes * n_queries);
+    if (rc) return rc;
+    {
+        DeviceGuard g(s->owner_device);
+        CU(cudaMemsetAsync(s->d_acc, 0, row_bytes * n_queries, s->stream));
+        CU(cudaEventRecord(s->zeroed, s->stream));
+    }
+    for (size_t i = 0; i < s->shards.size(); i++) {
+        pir_db* db = s->shards[i];
+        std::lock_guard<std::mutex> lkdb(db->mu);
+        DeviceGuard g(db->device);
+        CU(cudaStreamWaitEvent(db->stream, s->zeroed, 0));
+        for (uint32_t k = 0; k < n_queries; k++) {
+            if (qs[k].group_size != W || qs[k].is_keyword != qs[0].is_keyword)
+                return fail(PIR_ERR_BAD_ARG, "all queries of a batch must share group_size and is_keyword");
+            QueryGeom geom;
+            if ((rc = query_geom(db, &qs[k], &geom))) return rc;
+            if ((rc = enqueue_answer(db, &qs[k], geom, s->d_acc + (uint64_t)k * row_bytes, db->stream, false))) return rc;
+        }
+        CU(cudaEventRecord(s->done[i], db->stream));
+    }
+    {
+        DeviceGuard g(s->owner_device);
+        for (size_t i = 0; i < s->shards.size(); i++) CU(cudaStreamWaitEvent(s->stream, s->done[i], 0));
+        CU(cudaMemcpyAsync(s->h_acc, s->d_acc, row_bytes * n_queries, cudaMemcpyDeviceToHost, s->stream));
+        CU(cudaStreamSynchronize(s->stream));
+    }
+    for (uint32_t k = 0; k < n_queries; k++)
+        for (uint32_t c = 0; c < W; c++)
+            memcpy((uint8_t*)out + (size_t)k * ans + (size_t)c * s->slot_bytes,
+                   s->h_acc + (uint64_t)k * row_bytes + (uint64_t)c * s->pitch, s->slot_bytes);
+    return PIR_OK;
+}
+
+extern "C" int pir_server_answer(pir_server* s, const pir_query* q, void* out, size_t out_len) {
+    return pir_server_answer_batch(s, q, 1, out, out_len);
 }

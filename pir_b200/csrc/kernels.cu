@@ -511,4 +511,43 @@ cudaError_t launch_synth_fill(uint8_t* db, uint64_t slot_begin, uint64_t n_slots
     return cudaGetLastError();
 }
 
+// ---- multi-GPU combine signalling --------------------------------------------------
+// A shard's answer kernel XORs its partial straight into the combine slot (possibly a peer GPU's memory,
+// red.global.xor over NVLink).  signal_arrival runs after it on the same stream: the partial is complete,
+// so it bumps the slot's arrival counter with system scope.  wait_arrivals runs on the OWNER GPU only and
+// spins (bounded) until all shards have arrived; the waiting kernel and the signalling kernels run on
+// different GPUs, so none of them can starve the other.
+__global__ void signal_arrival_kernel(uint32_t* arrivals) {
+    __threadfence_system();
+    atomicAdd_system(arrivals, 1u);
+}
+
+__global__ void wait_arrivals_kernel(const uint32_t* arrivals, uint32_t expected, uint64_t timeout_cycles,
+                                     uint32_t* timed_out) {
+    const long long t0 = clock64();
+    while (true) {
+        uint32_t v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(arrivals) : "memory");
+        if (v >= expected) break;
+        if ((uint64_t)(clock64() - t0) > timeout_cycles) {
+            *timed_out = 1u;
+            break;
+        }
+        __nanosleep(200);
+    }
+}
+
+cudaError_t launch_signal_arrival(uint32_t* arrivals, cudaStream_t st) {
+    signal_arrival_kernel<<<1, 1, 0, st>>>(arrivals);
+    g_launches++;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_wait_arrivals(const uint32_t* arrivals, uint32_t expected, uint64_t timeout_cycles,
+                                 uint32_t* timed_out, cudaStream_t st) {
+    wait_arrivals_kernel<<<1, 1, 0, st>>>(arrivals, expected, timeout_cycles, timed_out);
+    g_launches++;
+    return cudaGetLastError();
+}
+
 }  // namespace pirb

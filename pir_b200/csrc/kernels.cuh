@@ -81,6 +81,11 @@ cudaError_t configure_answer_kernel();
 cudaError_t launch_answer(const QueryConst& qc, const AnswerPlan& ap, const uint32_t* d_t0, uint32_t smem_base,
                           int num_sms, cudaStream_t st);
 
+// multi-GPU combine signalling: bump / wait for a slot's arrival counter (system scope)
+cudaError_t launch_signal_arrival(uint32_t* arrivals, cudaStream_t st);
+cudaError_t launch_wait_arrivals(const uint32_t* arrivals, uint32_t expected, uint64_t timeout_cycles,
+                                 uint32_t* timed_out, cudaStream_t st);
+
 uint64_t launch_count();
 void count_launch();
 

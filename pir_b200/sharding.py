@@ -58,3 +58,106 @@ def gather_and_combine(partial, dist, dst=0):
     if parts is None:
         return None
     return xor_combine(parts)
+
+
+class Server:
+    """One PIR server whose database is row-sharded over several GPUs, driven from ONE process
+    (pir_server_* in include/pir_b200.h).  Every shard's kernel XORs its partial answer into a single
+    accumulator on devices[0] (peer stores over NVLink); there is no combine pass and no NCCL."""
+
+    def __init__(self, devices, db_size, slot_bytes, shard_align=1):
+        self.L = _capi.lib()
+        self.db_size, self.slot_bytes = db_size, slot_bytes
+        arr = (C.c_int * len(devices))(*devices)
+        self.h = C.c_void_p()
+        _capi.check(self.L.pir_server_create(arr, len(devices), db_size, slot_bytes, shard_align, C.byref(self.h)))
+
+    @property
+    def num_shards(self):
+        return self.L.pir_server_num_shards(self.h)
+
+    def shard(self, i):
+        db = C.c_void_p()
+        _capi.check(self.L.pir_server_shard(self.h, i, C.byref(db)))
+        return db
+
+    def upload(self, dense, slot_index=0):
+        dense = np.ascontiguousarray(dense, dtype=np.uint8)
+        _capi.check(self.L.pir_server_upload(self.h, slot_index, dense.ctypes.data_as(C.c_void_p),
+                                             dense.size // self.slot_bytes))
+
+    def fill_synthetic(self, seed):
+        _capi.check(self.L.pir_server_fill_synthetic(self.h, seed))
+
+    def answer(self, q):
+        n = q.group_size * self.slot_bytes
+        out = np.zeros(n, dtype=np.uint8)
+        _capi.check(self.L.pir_server_answer(self.h, C.byref(q), out.ctypes.data_as(C.c_void_p), n))
+        return out
+
+    def answer_batch(self, qs):
+        n = qs[0].group_size * self.slot_bytes
+        arr = (_capi.PirQuery * len(qs))(*qs)
+        out = np.zeros(n * len(qs), dtype=np.uint8)
+        _capi.check(self.L.pir_server_answer_batch(self.h, arr, len(qs), out.ctypes.data_as(C.c_void_p), out.size))
+        return out.reshape(len(qs), n)
+
+    def close(self):
+        if self.h:
+            self.L.pir_server_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
+class Combine:
+    """Ring of combine slots for the one-process-per-GPU launch (pir_combine_* in include/pir_b200.h).
+    The owner rank creates and exports; the others open the CUDA IPC handle."""
+
+    def __init__(self, device, n_slots, slot_stride, handle=None):
+        self.L = _capi.lib()
+        self.n_slots, self.stride, self.owner = n_slots, slot_stride, handle is None
+        self.h = C.c_void_p()
+        if handle is None:
+            _capi.check(self.L.pir_combine_create(device, n_slots, slot_stride, C.byref(self.h)))
+        else:
+            buf = (C.c_uint8 * _capi.PIR_IPC_HANDLE_BYTES).from_buffer_copy(bytes(handle))
+            _capi.check(self.L.pir_combine_open(device, buf, n_slots, slot_stride, C.byref(self.h)))
+
+    def export(self):
+        buf = (C.c_uint8 * _capi.PIR_IPC_HANDLE_BYTES)()
+        _capi.check(self.L.pir_combine_export(self.h, buf))
+        return bytes(buf)
+
+    def reset(self, first=0, count=None):
+        _capi.check(self.L.pir_combine_reset(self.h, first, self.n_slots - first if count is None else count))
+
+    def accumulate(self, db, q, slot, stream=None):
+        _capi.check(self.L.pir_answer_accumulate_device(db, C.byref(q), self.h, slot, stream))
+
+    def wait_read(self, slot, expected, nbytes, timeout_ms=10000):
+        out = np.zeros(nbytes, dtype=np.uint8)
+        _capi.check(self.L.pir_combine_wait_read(self.h, slot, expected, out.ctypes.data_as(C.c_void_p), nbytes,
+                                                 timeout_ms))
+        return out
+
+    def close(self):
+        if self.h:
+            self.L.pir_combine_destroy(self.h)
+            self.h = None
+
+
+def open_combine_over_group(dist, device, n_slots, slot_stride, owner=0):
+    """Rendezvous of the IPC handle over an existing torch.distributed group (plumbing only: 64 bytes,
+    once).  Returns this rank's Combine."""
+    rank = dist.get_rank()
+    comb = Combine(device, n_slots, slot_stride) if rank == owner else None
+    box = [comb.export() if rank == owner else None]
+    dist.broadcast_object_list(box, src=owner)
+    if rank != owner:
+        comb = Combine(device, n_slots, slot_stride, handle=box[0])
+    return comb

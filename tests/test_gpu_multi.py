@@ -1,0 +1,146 @@
+"""GPU tests of the multi-GPU combine: pir_server (one process, all shards) and
+pir_combine (one process per GPU, CUDA IPC).  On a 1-GPU box the shards share device 0, which exercises
+the same sharding arithmetic, accumulate-without-zeroing kernels and arrival counters; with >= 2 GPUs the
+peer-store path over NVLink is covered too."""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+import pytest
+
+import oracle
+from pir_b200 import _capi, sharding
+from tests.helpers import Handle, make_queries
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _devices(gpu_lib, n):
+    have = gpu_lib.pir_device_count()
+    return [i % have for i in range(n)]
+
+
+@pytest.mark.parametrize("n_shards,db_size,slot_bytes,W", [
+    (1, 5000, 32, 1), (2, 1 << 14, 256, 1), (3, 12345, 64, 2), (4, 3000, 100, 3), (8, 1 << 15, 32, 1),
+    (2, 1 << 12, 1024, 4), (5, 7, 16, 1),
+])
+def test_server_answer_matches_oracle(gpu_lib, n_shards, db_size, slot_bytes, W):
+    data = oracle.synth_fill(5, 0, db_size, slot_bytes)
+    rows = db_size // W
+    idx = (rows * 2) // 3
+    (o0, o1), (q0, q1) = make_queries(11, db_size, W, idx)
+    with sharding.Server(_devices(gpu_lib, n_shards), db_size, slot_bytes, shard_align=W) as srv:
+        assert srv.num_shards == n_shards
+        srv.fill_synthetic(5)
+        a0, a1 = srv.answer(q0), srv.answer(q1)
+        assert np.array_equal(a0, oracle.answer(o0, data, db_size, slot_bytes))
+        assert np.array_equal(a1, oracle.answer(o1, data, db_size, slot_bytes))
+        assert np.array_equal(a0 ^ a1, data[idx * W:(idx + 1) * W].reshape(-1))
+        both = srv.answer_batch([q0, q1, q0])
+        assert np.array_equal(both[0], a0) and np.array_equal(both[1], a1) and np.array_equal(both[2], a0)
+
+
+def test_server_upload_routes_to_shards(gpu_lib):
+    rng = np.random.default_rng(3)
+    db_size, S = 1000, 48
+    data = rng.integers(0, 256, size=(db_size, S), dtype=np.uint8)
+    (o0, _), (q0, _) = make_queries(4, db_size, 1, 777)
+    with sharding.Server(_devices(gpu_lib, 3), db_size, S) as srv:
+        srv.upload(data[:400], 0)
+        srv.upload(data[400:], 400)   # straddles shard boundaries
+        assert np.array_equal(srv.answer(q0), oracle.answer(o0, data, db_size, S))
+
+
+def test_combine_slots_single_process(gpu_lib):
+    """Two shard handles accumulate into ring slots of one combine buffer; the owner waits for both."""
+    n, S = 1 << 13, 256
+    data = oracle.synth_fill(9, 0, n, S)
+    comb = sharding.Combine(0, 4, S)
+    try:
+        with Handle(n, S, 0, n // 2) as h0, Handle(n, S, n // 2, n // 2) as h1:
+            h0.fill(9)
+            h1.fill(9)
+            for rep in range(2):  # second round re-uses the slots after a reset
+                for slot, idx in enumerate((5, 4097, 8000, 4095)):
+                    (o0, _), (q0, _) = make_queries(20 + slot + 10 * rep, n, 1, idx)
+                    comb.accumulate(h0.h, q0, slot)
+                    comb.accumulate(h1.h, q0, slot)
+                    got = comb.wait_read(slot, 2, S)
+                    assert np.array_equal(got, oracle.answer(o0, data, n, S)), (rep, slot)
+                comb.reset()
+    finally:
+        comb.close()
+
+
+def test_combine_wait_times_out(gpu_lib):
+    comb = sharding.Combine(0, 1, 64)
+    try:
+        with pytest.raises(_capi.PirError):
+            comb.wait_read(0, 1, 64, timeout_ms=20)
+        # the flag is cleared: a satisfied wait works afterwards
+        assert np.array_equal(comb.wait_read(0, 0, 64, timeout_ms=20), np.zeros(64, dtype=np.uint8))
+    finally:
+        comb.close()
+
+
+def _ipc_worker(rank, world, port, n, S, idx, q):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from pir_b200 import sharding as sh
+        from tests.helpers import Handle as H, make_queries as mq
+        import oracle as orc
+        comb = sh.open_combine_over_group(dist, rank, 2, S)
+        begin, count = sh.shard_slots(n, 1, rank, world)
+        with H(n, S, begin, count, device=rank) as h:
+            h.fill(13)
+            (o0, o1), (q0, q1) = mq(77, n, 1, idx)
+            comb.accumulate(h.h, q0, 0)
+            comb.accumulate(h.h, q1, 1)
+            if rank == 0:
+                a0 = comb.wait_read(0, world, S)
+                a1 = comb.wait_read(1, world, S)
+                data = orc.synth_fill(13, 0, n, S)
+                ok = bool(np.array_equal(a0, orc.answer(o0, data, n, S)) and
+                          np.array_equal(a1, orc.answer(o1, data, n, S)) and
+                          np.array_equal(a0 ^ a1, data[idx]))
+                q.put(ok)
+            dist.barrier()
+        if rank != 0:
+            comb.close()   # peers unmap before the owner frees
+        dist.barrier()
+        if rank == 0:
+            comb.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_combine_over_cuda_ipc_two_gpus(gpu_lib):
+    """One process per GPU: rank 1's kernel XORs into rank 0's memory through a CUDA IPC mapping."""
+    if gpu_lib.pir_device_count() < 2:
+        pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
+    import socket
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_ipc_worker, args=(r, 2, port, 1 << 14, 256, 9999, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=240)
+    for p in procs:
+        if p.is_alive():
+            p.kill()
+            pytest.fail("rank hung")
+        assert p.exitcode == 0
+    assert q.get(timeout=5) is True
