@@ -2,20 +2,25 @@
 // (db.go:68-174 + dpf/server.go:55-101 + slot.go:19-30), warp-specialised for sm_100a.
 //
 // One persistent CTA per SM, 16 "tree" warps + kScanWarps "scan" warps:
-//   tree warps   per CTA task (a subtree of 2^(B+D+1) rows): thread 0 walks from the last task's
-//                common ancestor to the task root, the CTA expands B levels breadth-first, then every
-//                thread walks its own 2^(D+1)-row subtree depth-first (sibling stack in shared
-//                memory) with the unrolled T-table AES of aes_unrolled.cuh.  The thread's selection
-//                bits (one 32-bit word) go to a double-buffered word array in shared memory.
+//   tree warps   per CTA task (an aligned subtree of 2^(B+d+1) rows, d <= 7): walk from the previous
+//                task's common ancestor to the task root, expand B levels breadth-first to 2^B thread
+//                roots, then every thread walks its own 2^(d+1)-row subtree depth-first (sibling stack in
+//                shared memory) with the unrolled T-table AES of aes_unrolled.cuh.  Selection bits are
+//                published in SLICES of 8 rows per thread into a ring of word buffers in shared memory.
 //                Tree warps never touch global memory in the steady state.
-//   scan warps   turn the words into a compact list of selected rows (popc prefix sum per 32 words)
-//                and stream exactly those rows from HBM with coalesced 128-bit loads (32/c rows per
-//                warp load for rows of c 16-byte chunks), XOR-accumulating in registers; rows whose
+//   scan warps   turn a slice's words into a compact list of selected rows (popc prefix sum per 32
+//                words) and stream exactly those rows from HBM with coalesced 128-bit loads (32/c rows
+//                per warp load for rows of c 16-byte chunks), XOR-accumulating in registers; rows whose
 //                bit is 0 are never fetched (like db.go:93).  Loads go straight to registers: the
 //                shared-memory pipe is the kernel's bottleneck (AES table lookups), so staging rows
 //                through shared memory (TMA / cp.async) would cost more than it hides.
-// Hand-off uses four named barriers (full/empty per buffer).  The answer is reduced per CTA and
-// XORed into global memory with one atomic per word.
+// Hand-off is a producer/consumer ring of kRing slice buffers guarded by mbarriers (full: 16 tree warps
+// arrive, empty: the scan warps arrive).  The answer is reduced per CTA and XORed into global memory
+// (possibly a peer GPU's) with one atomic per word.
+//
+// Why deep tasks: the top of a task (walk + breadth-first levels) is executed by few warps and is bound
+// by single-warp issue latency (~1.7k cycles per level, ~28k cycles per task, measured), during which the
+// lookup pipe idles.  A thread that owns 2^(d+1) rows amortises it over 2^(d+1)-1 depth-first nodes.
 #include "kernels.cuh"
 #include "aes_unrolled.cuh"
 
@@ -24,26 +29,58 @@ namespace pirb {
 extern __shared__ __align__(16) uint8_t g_smem2[];
 
 constexpr int kTreeThreads = 512;
+constexpr int kTreeWarps = kTreeThreads / 32;
 constexpr int kScanWarps = 4;
 constexpr int kAnswerThreads = kTreeThreads + 32 * kScanWarps;
-constexpr int kV2MaxDepth = 4;                 // one 32-bit word of selection bits per thread
-constexpr uint32_t kListEntries = 1024;        // rows selected out of 32 words, per scan warp
-constexpr uint32_t kListBytes = kScanWarps * kListEntries * 2;
+constexpr int kV2MaxDepth = 7;                 // a thread owns at most 2^8 rows (sibling stack: 7 x 16 B)
+constexpr uint32_t kSliceLog = 3;              // rows per thread per slice (8), fewer for tiny depths
+constexpr uint32_t kRing = 8;                  // slice buffers in flight between tree and scan warps
+constexpr uint32_t kListEntries = 256;         // rows selected out of 32 words of a slice, per warp
+constexpr uint32_t kMaxTasks = 512;            // per CTA (launch_answer sizes the grid accordingly)
 
-// scratch layout below the tables (offsets from the dynamic shared memory base)
-constexpr uint32_t kOffStack = 0;                                   // [D<=4][4][512] u32 = 32 KB (aliases BFS)
+// scratch below the tables (offsets from the dynamic shared memory base)
+constexpr uint32_t kOffStack = 0;                                   // [D<=7][4][512] u32 = 56 KB (aliases BFS)
 constexpr uint32_t kOffBfsS = 0;                                    // [2][512] uint4    = 16 KB
 constexpr uint32_t kOffBfsT = 16384;                                // [2][512] u8       =  1 KB
-constexpr uint32_t kOffWords = 32768;                               // [2][512] u32      =  4 KB
-constexpr uint32_t kOffPathS = kOffWords + 4096;                    // [65] uint4
+constexpr uint32_t kOffPathS = kV2MaxDepth * 4 * kTreeThreads * 4;  // [65] uint4
 constexpr uint32_t kOffPathT = kOffPathS + 65 * 16;                 // [65] u32
 constexpr uint32_t kOffRed = kOffPathT + 65 * 4 + 12;               // [128] u32
-constexpr uint32_t kScratchEnd = kOffRed + 512;
+constexpr uint32_t kOffTasks = kOffRed + 512;                       // [1 + kMaxTasks] u32
+constexpr uint32_t kScratchEnd = kOffTasks + 4 + 4 * kMaxTasks;
+// above the tables (absolute shared-window addresses)
+constexpr uint32_t kAbsLists = kTableEnd;                                      // [20 warps][256] u16
+constexpr uint32_t kAbsRing = kAbsLists + (kAnswerThreads / 32) * kListEntries * 2;  // [kRing][512] u32
+constexpr uint32_t kAbsBars = kAbsRing + kRing * kTreeThreads * 4;             // full[kRing], empty[kRing] u64
+constexpr uint32_t kAbsClaim = kAbsBars + 2 * kRing * 8;                       // claim counter, done[kRing] u32
+constexpr uint32_t kSmemEnd = kAbsClaim + 4 * (1 + kRing) + 12;
 
-enum : int { BAR_TREE = 1, BAR_FULL0 = 2, BAR_EMPTY0 = 4, BAR_SCAN = 6 };
+enum : int { BAR_TREE = 1 };
 
 __device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
-__device__ __forceinline__ void bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+
+// ---- mbarrier ring ----------------------------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(uint32_t addr, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(addr), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t addr) {
+    asm volatile("mbarrier.arrive.release.cta.shared::cta.b64 _, [%0];" ::"r"(addr) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t addr, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.acquire.cta.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(addr), "r"(parity) : "memory");
+}
+__device__ __forceinline__ uint32_t full_bar(uint32_t slot) { return kAbsBars + slot * 8u; }
+__device__ __forceinline__ uint32_t empty_bar(uint32_t slot) { return kAbsBars + (kRing + slot) * 8u; }
+__device__ __forceinline__ uint32_t* ring_words(uint32_t slot) {
+    return reinterpret_cast<uint32_t*>(g_smem2 + (kAbsRing - smem_addr(g_smem2))) + slot * kTreeThreads;
+}
 
 __device__ __forceinline__ uint4 ldg_nc_v4(const uint8_t* p) {
     uint4 v;
@@ -62,7 +99,10 @@ __device__ __forceinline__ uint32_t range_mask32(uint64_t rowbase, uint32_t rw, 
     return hi & ~lo;
 }
 
-// ---- scan: selected rows of 32 words -> registers -------------------------------------------------
+// rows per thread per slice (log2) for a task of depth d: 8, or all 2^(d+1) rows when there are fewer
+__device__ __forceinline__ uint32_t slice_log(uint32_t d) { return d + 1u < kSliceLog ? d + 1u : kSliceLog; }
+
+// ---- scan: selected rows of 32 words of a slice -> registers ----------------------------------------
 struct ScanLane {
     uint32_t rpl, h, c;
     const uint8_t* lane_db;  // db + this lane's 16-byte chunk
@@ -79,17 +119,16 @@ __device__ __forceinline__ ScanLane scan_lane(const AnswerPlan& ap) {
     return sl;
 }
 
-// XOR the selected rows of words [g*32, g*32+32) of one task buffer into acc.  `list` is a private
-// 2 KB scratch of the calling warp.
+// XOR the selected rows of words [g*32, g*32+32) of one slice buffer into acc.  Word `i` of the buffer
+// holds thread i's selection bits for its rows [slice_off, slice_off + 2^slice_log) of the task
+// (thread i owns task rows [i << rows_log, (i+1) << rows_log)).  `list` is a private 512-byte scratch of
+// the calling warp.
 template <int UNROLL>
 __device__ __forceinline__ void scan_group(const AnswerPlan& ap, const ScanLane& sl, const uint32_t* wbuf,
-                                           uint32_t g, uint64_t p, uint16_t* list, uint4& acc) {
-    const uint32_t lane = threadIdx.x & 31u, rows_log = ap.D + 1;
-    // byte address of task row 0; rows before first_row are never selected
-    const int64_t task_row0 = (int64_t)((p << ap.B) << rows_log) - (int64_t)ap.first_row;
-    const uint8_t* tbase = sl.lane_db + task_row0 * (int64_t)ap.row_bytes;
-    const uint32_t widx = g * 32u + lane;
-    uint32_t w = wbuf[widx];
+                                           uint32_t g, int64_t task_row0, uint32_t rows_log, uint32_t slice_off,
+                                           uint16_t* list, uint4& acc) {
+    const uint32_t lane = threadIdx.x & 31u;
+    uint32_t w = wbuf[g * 32u + lane];
     const uint32_t cnt = __popc(w);
     uint32_t pre = cnt;
 #pragma unroll
@@ -98,8 +137,12 @@ __device__ __forceinline__ void scan_group(const AnswerPlan& ap, const ScanLane&
         if (lane >= (uint32_t)o) pre += v;
     }
     const uint32_t total = __shfl_sync(0xffffffffu, pre, 31);
+    if (total == 0) return;
+    // byte address of the group's first row, for this lane's 16-byte chunk (rows before the shard's
+    // first row are never selected, so a negative offset is never dereferenced)
+    const uint8_t* gbase = sl.lane_db + (task_row0 + ((int64_t)(g * 32u) << rows_log)) * (int64_t)ap.row_bytes;
     uint32_t pos = pre - cnt;
-    const uint32_t rbase = widx << rows_log;
+    const uint32_t rbase = (lane << rows_log) + slice_off;
     while (w) {
         list[pos++] = (uint16_t)(rbase + (uint32_t)__ffs(w) - 1u);
         w &= w - 1u;
@@ -111,7 +154,7 @@ __device__ __forceinline__ void scan_group(const AnswerPlan& ap, const ScanLane&
         for (int u = 0; u < UNROLL; u++) {
             const uint32_t e = e0 + u * sl.rpl + sl.h;
             v[u] = make_uint4(0, 0, 0, 0);
-            if (e < total) v[u] = ldg_nc_v4(tbase + (uint64_t)list[e] * ap.row_bytes);
+            if (e < total) v[u] = ldg_nc_v4(gbase + (uint64_t)list[e] * ap.row_bytes);
         }
 #pragma unroll
         for (int u = 0; u < UNROLL; u += 2) {
@@ -140,8 +183,64 @@ __device__ __forceinline__ void fold_acc(const ScanLane& sl, uint4 acc) {
     }
 }
 
-constexpr uint32_t kGroups = kTreeThreads / 32;  // 32-word groups per task
+constexpr uint32_t kGroups = kTreeThreads / 32;  // 32-word groups per slice
 
+// ---- work split ---------------------------------------------------------------------------------------
+// The shard is cut into CHUNKS of 2^(B+Dmin+1) rows (a task whose threads own 2^(Dmin+1) rows each) and
+// CTA b owns the contiguous chunk range [b*C/G, (b+1)*C/G).  The CTA covers its range with aligned
+// power-of-two TASKS of 2^(B+d+1) rows, Dmin <= d <= Dmax, as large as alignment allows (binary
+// decomposition): most rows are expanded in deep tasks while the range boundaries sit on a fine grid, so
+// every CTA gets the same number of rows to within a chunk whatever the shard size.  Thread
+// kAnswerThreads-1 builds the CTA's task list once, smallest tasks first (whatever runs last is the part
+// whose scan is overlapped least, so the deep, many-slice tasks go last); both roles read it.
+struct TaskIter {
+    const uint32_t* list;  // shared: entry = (chunk offset from the CTA's first chunk) << 3 | d
+    uint64_t chunk0;
+    uint32_t n, pos, chunk_log;
+    __device__ __forceinline__ TaskIter(const AnswerPlan& ap, const uint32_t* task_list) {
+        list = task_list + 1;
+        n = task_list[0];
+        pos = 0;
+        chunk_log = ap.B + ap.Dmin + 1u;
+        const uint64_t end_row = ap.first_row + ap.n_rows;
+        const uint64_t cf = ap.first_row >> chunk_log, cl = (end_row + ((1ull << chunk_log) - 1ull)) >> chunk_log;
+        chunk0 = cf + (uint64_t)blockIdx.x * (cl - cf) / gridDim.x;
+    }
+    __device__ __forceinline__ bool next(uint64_t& row_start, uint32_t& d) {
+        if (pos >= n) return false;
+        const uint32_t e = list[pos++];
+        d = e & 7u;
+        row_start = (chunk0 + (e >> 3)) << chunk_log;
+        return true;
+    }
+    __device__ __forceinline__ bool exhausted() const { return pos >= n; }
+};
+
+__device__ __forceinline__ void build_task_list(const AnswerPlan& ap, uint32_t* task_list) {
+    const uint32_t chunk_log = ap.B + ap.Dmin + 1u;
+    const uint64_t end_row = ap.first_row + ap.n_rows;
+    const uint64_t cf = ap.first_row >> chunk_log, cl = (end_row + ((1ull << chunk_log) - 1ull)) >> chunk_log;
+    const uint64_t C = cl - cf;
+    const uint64_t c0 = cf + (uint64_t)blockIdx.x * C / gridDim.x, c1 = cf + (uint64_t)(blockIdx.x + 1) * C / gridDim.x;
+    uint32_t n = 0;
+    for (uint32_t want = ap.Dmin; want <= ap.D; want++) {
+        uint64_t cur = c0;
+        while (cur < c1) {
+            uint32_t d = ap.Dmin;
+            uint64_t span = 1;
+            while (d < ap.D && !(cur & (2ull * span - 1ull)) && cur + 2ull * span <= c1) {
+                d++;
+                span *= 2ull;
+            }
+            if (d == want) {
+                if (n >= kMaxTasks) __trap();  // launch_answer sizes the grid so that this cannot happen
+                task_list[1 + n++] = ((uint32_t)(cur - c0) << 3) | d;
+            }
+            cur += span;
+        }
+    }
+    task_list[0] = n;
+}
 // ---- cooperative node expansion for the narrow top of a task --------------------------------------
 // One warp executing a whole 3-block PRG is bound by its own SMSP's ALU rate (~2500 cycles per level).
 // Near the root only a few nodes exist, so three warps on three SMSPs each take ONE AES block of the
@@ -187,31 +286,88 @@ __device__ __forceinline__ void coop_block(const QueryConst& qc, uint32_t k, uin
 
 constexpr uint32_t kCoopMaxLevel = 6;  // breadth-first levels with <= 64 nodes use coop_block
 
+// ---- consumer loop (scan warps all along, tree warps once they have nothing left to expand) ----------
+// Work unit = one 32-word group of one slice, claimed in order from a shared counter, so the backlog at
+// the end of the kernel is drained by all 20 warps.  The warp that completes a slice's last group hands
+// the ring slot back to the tree warps.
+__device__ __forceinline__ void consume_slices(const AnswerPlan& ap, uint32_t warp_in_cta) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const ScanLane sl = scan_lane(ap);
+    const uint32_t dyn_base = smem_addr(g_smem2);
+    uint16_t* list = reinterpret_cast<uint16_t*>(g_smem2 + (kAbsLists - dyn_base)) + warp_in_cta * kListEntries;
+    uint32_t* claim = reinterpret_cast<uint32_t*>(g_smem2 + (kAbsClaim - dyn_base));
+    uint32_t* done = claim + 1;
+    const uint32_t* task_list = reinterpret_cast<const uint32_t*>(g_smem2 + kOffTasks);
+    TaskIter ti(ap, task_list);
+    uint64_t row_start = 0;
+    uint32_t D = 0;
+    uint32_t gs0 = 0, gs1 = 0;  // global slice range of the current task
+    uint4 acc = make_uint4(0, 0, 0, 0);
+    while (true) {
+        uint32_t u = 0;
+        if (lane == 0) u = atomicAdd(claim, 1u);
+        u = __shfl_sync(0xffffffffu, u, 0);
+        const uint32_t gsl = u / kGroups, g = u % kGroups;
+        bool have = true;
+        while (gsl >= gs1) {  // advance to the task that owns this slice
+            if (!ti.next(row_start, D)) {
+                have = false;
+                break;
+            }
+            gs0 = gs1;
+            gs1 += 1u << (D + 1u - slice_log(D));
+        }
+        if (!have) break;
+        const uint32_t slot = gsl & (kRing - 1u), par = (gsl / kRing) & 1u;
+        mbar_wait(full_bar(slot), par);
+        const uint32_t slog = slice_log(D);
+        scan_group<16>(ap, sl, ring_words(slot), g, (int64_t)row_start - (int64_t)ap.first_row, D + 1u,
+                       (gsl - gs0) << slog, list, acc);
+        __syncwarp();
+        if (lane == 0) {
+            __threadfence_block();
+            if (atomicAdd(&done[slot], 1u) == kGroups - 1u) {
+                done[slot] = 0u;
+                mbar_arrive(empty_bar(slot));
+            }
+        }
+    }
+    fold_acc(sl, acc);
+}
+
 // ---- tree role ------------------------------------------------------------------------------------
-__device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan& ap, uint32_t lc) {
-    const uint32_t tid = threadIdx.x, warp = tid >> 5;
-    const uint32_t D = ap.D, B = ap.B, Fc = ap.Fc;
-    const uint32_t lvl0 = Fc + B;
-    const uint32_t RW = 2u << D;
-    const uint32_t nlp = 1u << D;
-    const uint32_t rows_log = D + 1;
-    const uint64_t end_row = ap.first_row + ap.n_rows;
+__device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan& ap, uint32_t lc, long long c_entry) {
+    const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31u;
+    const uint32_t B = ap.B;
+    const uint32_t top_bits = qc.num_bits - 1u;  // rows are (num_bits-1)-bit numbers: the top level always goes left
+    const uint64_t first_row = ap.first_row, end_row = ap.first_row + ap.n_rows;
     uint32_t* stk = reinterpret_cast<uint32_t*>(g_smem2 + kOffStack);
     uint4* bfs_s = reinterpret_cast<uint4*>(g_smem2 + kOffBfsS);
     uint8_t* bfs_t = g_smem2 + kOffBfsT;
-    uint32_t* words = reinterpret_cast<uint32_t*>(g_smem2 + kOffWords);
     uint4* path_s = reinterpret_cast<uint4*>(g_smem2 + kOffPathS);
     uint8_t* path_t = g_smem2 + kOffPathT;
 
-    // contiguous block of tasks for this CTA
-    const uint64_t k0 = (uint64_t)blockIdx.x * ap.task_count / gridDim.x;
-    const uint64_t k1 = (uint64_t)(blockIdx.x + 1) * ap.task_count / gridDim.x;
-    uint64_t p_prev = 0;
-    for (uint64_t k = k0; k < k1; k++) {
-        const uint32_t it = (uint32_t)(k - k0), buf = it & 1u;
-        const uint64_t p = ap.task_first + k;  // node index at level Fc
-        // -- top walk: re-expand from the common ancestor with the previous task's root (3 threads) --
-        const uint32_t ck = warp & 3u, cj = (warp >> 2) * 32u + (tid & 31u);  // coop role: block ck of node cj
+    TaskIter ti(ap, reinterpret_cast<const uint32_t*>(g_smem2 + kOffTasks));
+    uint64_t row_start = 0, row_prev = 0;
+    uint32_t D = 0, Fc_prev = 0, it = 0;
+    uint32_t gs = 0;  // slices published so far (ring position)
+    long long c_top = 0, c_bfs = 0, c_dfs = 0, c_tail = 0, c_pub = 0, c_mark = clock64();
+    const long long c_begin = c_mark;
+#define PHASE(acc)                              \
+    if (ap.dbg && tid == 0) {                   \
+        const long long now_ = clock64();       \
+        acc += now_ - c_mark;                   \
+        c_mark = now_;                          \
+    }
+    while (ti.next(row_start, D)) {
+        const uint32_t Fc = top_bits - D - B;        // tree level of the task root
+        const uint32_t lvl0 = Fc + B;
+        const uint32_t nlp = 1u << D;                // leaf parents per thread
+        const uint32_t rows_log = D + 1;
+        const uint32_t slog = slice_log(D), lp_log = slog - 1u;
+        const uint64_t p = row_start >> (B + rows_log);  // node index at level Fc
+        // -- top walk: re-expand from the common ancestor with the previous task's root (3 warps) --
+        const uint32_t ck = warp & 3u, cj = (warp >> 2) * 32u + lane;  // coop role: block ck of node cj
         const bool coop_warp = ck < 3u && warp < 8u;
         {
             uint32_t cp = 0;
@@ -222,7 +378,11 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
                 }
                 bar_sync(BAR_TREE, kTreeThreads);
             } else {
-                cp = Fc - (64u - (uint32_t)__clzll((long long)(p ^ p_prev)));
+                // levels whose path entries are still valid: the common prefix of the two first rows,
+                // capped by how deep the previous and the current walk go
+                cp = top_bits - (64u - (uint32_t)__clzll((long long)(row_start ^ row_prev)));
+                cp = cp < Fc_prev ? cp : Fc_prev;
+                cp = cp < Fc ? cp : Fc;
             }
             for (uint32_t l = cp; l < Fc; l++) {
                 if (coop_warp && cj == 0) {
@@ -238,8 +398,10 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
                 bfs_t[0] = path_t[Fc];
             }
         }
-        p_prev = p;
+        row_prev = row_start;
+        Fc_prev = Fc;
         bar_sync(BAR_TREE, kTreeThreads);
+        PHASE(c_top)
         // -- B breadth-first levels: 2^B thread roots --
         for (uint32_t b = 0; b < B; b++) {
             const uint32_t o = ((b + 1) & 1) * kTreeThreads;
@@ -269,14 +431,29 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
             t = bfs_t[(B & 1) * kTreeThreads + tid];
         }
         bar_sync(BAR_TREE, kTreeThreads);  // the sibling stack aliases the BFS buffers
+        PHASE(c_bfs)
 
-        const uint64_t f = (p << B) + tid;  // this thread's subtree root at level lvl0
-        const uint64_t rowbase = f << rows_log;
+        const uint64_t rowbase = ((p << B) + tid) << rows_log;  // this thread's first row
         const uint64_t warp_row0 = ((p << B) + (tid & ~31u)) << rows_log;
         const uint64_t warp_row1 = ((p << B) + (tid & ~31u) + 32u) << rows_log;
-        uint32_t word = 0;
-        const bool warp_live = (warp * 32u < (1u << B)) && warp_row0 < end_row && warp_row1 > ap.first_row;
-        if (warp_live) {
+        const bool warp_live = (warp * 32u < (1u << B)) && warp_row0 < end_row && warp_row1 > first_row;
+        const bool inside = row_start >= first_row && row_start + (1ull << (B + rows_log)) <= end_row;
+        const uint32_t n_slices = 1u << (rows_log - slog);
+        // publish one slice: wait until the scan warps have drained the ring slot, store, arrive
+#define PUBLISH(word_)                                                              \
+    {                                                                               \
+        const uint32_t slot_ = gs & (kRing - 1u), par_ = (gs / kRing) & 1u;         \
+        const long long w0_ = (ap.dbg && tid == 0) ? clock64() : 0;                 \
+        mbar_wait(empty_bar(slot_), par_ ^ 1u);                                     \
+        if (ap.dbg && tid == 0) c_pub += clock64() - w0_;                           \
+        ring_words(slot_)[tid] = (word_);                                           \
+        __syncwarp();                                                               \
+        if (lane == 0) mbar_arrive(full_bar(slot_));                                \
+        gs++;                                                                       \
+    }
+        if (!warp_live) {
+            for (uint32_t q = 0; q < n_slices; q++) PUBLISH(0u)
+        } else {
             uint32_t tst = 0, d = 0, i = 0, bw = 0;
             while (true) {
                 const uint32_t lvl = lvl0 + d;
@@ -296,78 +473,65 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
                     d++;
                     continue;
                 }
-                bw |= leaf_parent_tail(qc, a, s, t, cw, cwtl, cwtr, lc) << (2u * i);
+                bw |= leaf_parent_tail(qc, a, s, t, cw, cwtl, cwtr, lc) << (2u * (i & ((1u << lp_log) - 1u)));
                 i++;
+                if ((i & ((1u << lp_log) - 1u)) == 0) {  // a slice of every thread's rows is final: publish it
+                    const uint32_t q = (i >> lp_log) - 1u;
+                    uint32_t m = active ? 0xffffffffu : 0u;
+                    if (!inside) m = active ? range_mask32(rowbase + ((uint64_t)q << slog), 1u << slog, first_row, end_row) : 0u;
+                    PUBLISH(bw & m)
+                    bw = 0;
+                }
                 if (i == nlp) break;
                 d = D - (uint32_t)(__ffs(i) - 1);  // next subtree root: the sibling stacked at that depth
 #pragma unroll
                 for (int w = 0; w < 4; w++) s[w] = stk[((d - 1) * 4 + w) * kTreeThreads + tid];
                 t = (tst >> (d - 1)) & 1u;
             }
-            word = active ? (bw & range_mask32(rowbase, RW, ap.first_row, end_row)) : 0u;
         }
-        if (it >= 2) bar_sync(BAR_EMPTY0 + buf, kAnswerThreads);  // scan warps are done with this buffer
-        words[buf * kTreeThreads + tid] = word;
-        __threadfence_block();
-        bar_arrive(BAR_FULL0 + buf, kAnswerThreads);
-        if (k + 1 == k1) {
-            // last task of this CTA: nothing left to expand, so the tree warps scan groups
-            // [kScanWarps, kGroups) themselves (row lists in the now idle sibling stack)
-            bar_sync(BAR_TREE, kTreeThreads);
-            const ScanLane sl = scan_lane(ap);
-            uint4 acc = make_uint4(0, 0, 0, 0);
-            uint16_t* list = reinterpret_cast<uint16_t*>(g_smem2 + kOffStack) + warp * kListEntries;
-            for (uint32_t g = kScanWarps + warp; g < kGroups; g += kTreeThreads / 32)
-                scan_group<8>(ap, sl, words + buf * kTreeThreads, g, p, list, acc);
-            fold_acc(sl, acc);
-        }
+#undef PUBLISH
+        PHASE(c_dfs)
+        it++;
     }
-    // drain the scan warps' last "empty" arrivals so that no barrier is left half-complete
-    const uint32_t ntask = (uint32_t)(k1 - k0);
-    if (ntask >= 2) bar_sync(BAR_EMPTY0 + (ntask & 1u), kAnswerThreads);
-    if (ntask >= 1) bar_sync(BAR_EMPTY0 + ((ntask - 1) & 1u), kAnswerThreads);
-}
-
-// ---- scan role ------------------------------------------------------------------------------------
-__device__ __forceinline__ void scan_role(const AnswerPlan& ap) {
-    const uint32_t sw = (threadIdx.x - kTreeThreads) >> 5;
-    const ScanLane sl = scan_lane(ap);
-    const uint32_t* words = reinterpret_cast<const uint32_t*>(g_smem2 + kOffWords);
-    const uint32_t dyn_base = smem_addr(g_smem2);
-    uint16_t* list = reinterpret_cast<uint16_t*>(g_smem2 + (kTableEnd - dyn_base)) + sw * kListEntries;  // above the tables
-    uint4 acc = make_uint4(0, 0, 0, 0);
-    const uint64_t k0 = (uint64_t)blockIdx.x * ap.task_count / gridDim.x;
-    const uint64_t k1 = (uint64_t)(blockIdx.x + 1) * ap.task_count / gridDim.x;
-    for (uint64_t k = k0; k < k1; k++) {
-        const uint32_t buf = (uint32_t)(k - k0) & 1u;
-        bar_sync(BAR_FULL0 + buf, kAnswerThreads);
-        // the tree warps help with the CTA's last task (they have nothing left to expand): groups
-        // [0, kScanWarps) stay here, the rest is theirs
-        const uint32_t gend = (k + 1 == k1) ? (uint32_t)kScanWarps : kGroups;
-        for (uint32_t g = sw; g < gend; g += kScanWarps)
-            scan_group<16>(ap, sl, words + buf * kTreeThreads, g, ap.task_first + k, list, acc);
-        bar_arrive(BAR_EMPTY0 + buf, kAnswerThreads);
+    // nothing left to expand: help the scan warps drain the ring
+    consume_slices(ap, warp);
+    PHASE(c_tail)
+#undef PHASE
+    if (ap.dbg && tid == 0) {
+        unsigned long long* o = ap.dbg + 8ull * blockIdx.x;
+        o[0] = (unsigned long long)c_top; o[1] = (unsigned long long)c_bfs; o[2] = (unsigned long long)c_pub;
+        o[3] = (unsigned long long)c_dfs; o[4] = (unsigned long long)c_tail; o[5] = (unsigned long long)(clock64() - c_begin);
+        o[6] = it; o[7] = (unsigned long long)(c_begin - c_entry);
     }
-    fold_acc(sl, acc);
 }
 
 __global__ void __launch_bounds__(kAnswerThreads, 1)
 answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ AnswerPlan ap,
               const uint32_t* __restrict__ t0) {
+    const uint32_t base = smem_addr(g_smem2);
+    const long long c_entry = clock64();
     {
-        const uint32_t base = smem_addr(g_smem2);
         uint32_t dyn;
         asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dyn));
-        if (base + dyn < kTableEnd + kListBytes || base + kScratchEnd > kTableBase) __trap();
+        if (base + dyn < kSmemEnd || base + kScratchEnd > kTableBase) __trap();
     }
     fill_tables(t0);
     uint32_t* red = reinterpret_cast<uint32_t*>(g_smem2 + kOffRed);
     if (threadIdx.x < 128) red[threadIdx.x] = 0;
+    if (threadIdx.x == kAnswerThreads - 1) build_task_list(ap, reinterpret_cast<uint32_t*>(g_smem2 + kOffTasks));
+    if (threadIdx.x == kAnswerThreads - 2) {
+        for (uint32_t k = 0; k < kRing; k++) {
+            mbar_init(full_bar(k), kTreeWarps);
+            mbar_init(empty_bar(k), 1);
+        }
+        uint32_t* claim = reinterpret_cast<uint32_t*>(g_smem2 + (kAbsClaim - base));
+        for (uint32_t k = 0; k < 1 + kRing; k++) claim[k] = 0;
+    }
     __syncthreads();
     if (threadIdx.x < kTreeThreads)
-        tree_role(qc, ap, lane_const());
+        tree_role(qc, ap, lane_const(), c_entry);
     else
-        scan_role(ap);
+        consume_slices(ap, threadIdx.x >> 5);
     __syncthreads();
     const uint32_t words_out = (uint32_t)(ap.row_bytes >> 2);
     if (threadIdx.x < words_out) {
@@ -382,15 +546,24 @@ bool answer_kernel_supports(uint64_t row_bytes, uint32_t D) {
 }
 
 cudaError_t configure_answer_kernel() {
-    return cudaFuncSetAttribute(answer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)(kTableEnd + kListBytes));
+    return cudaFuncSetAttribute(answer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemEnd);
+}
+
+uint64_t answer_chunks(uint64_t first_row, uint64_t n_rows, uint32_t B, uint32_t Dmin) {
+    const uint32_t cl = B + Dmin + 1u;
+    return ((first_row + n_rows + ((1ull << cl) - 1ull)) >> cl) - (first_row >> cl);
 }
 
 cudaError_t launch_answer(const QueryConst& qc, const AnswerPlan& ap, const uint32_t* d_t0, uint32_t smem_base,
                           int num_sms, cudaStream_t st) {
-    if (ap.task_count == 0) return cudaSuccess;
-    unsigned grid = (unsigned)(ap.task_count < (uint64_t)num_sms ? ap.task_count : (uint64_t)num_sms);
-    answer_kernel<<<grid, kAnswerThreads, kTableEnd + kListBytes - smem_base, st>>>(qc, ap, d_t0);
+    if (ap.n_rows == 0) return cudaSuccess;
+    const uint64_t chunks = answer_chunks(ap.first_row, ap.n_rows, ap.B, ap.Dmin);
+    uint64_t g = chunks < (uint64_t)num_sms ? chunks : (uint64_t)num_sms;
+    // a CTA's task list holds kMaxTasks entries and a task is at least one chunk: very large shards run
+    // more CTAs than SMs (in waves) rather than overflow it
+    const uint64_t gmin = (chunks + (kMaxTasks - 1)) / kMaxTasks;
+    if (g < gmin) g = gmin;
+    answer_kernel<<<(unsigned)g, kAnswerThreads, kSmemEnd - smem_base, st>>>(qc, ap, d_t0);
     count_launch();
     return cudaGetLastError();
 }

@@ -212,6 +212,9 @@ struct pir_db {
     uint64_t out_cap = 0;
     uint8_t* h_out = nullptr;  // pinned
     uint64_t h_out_cap = 0;
+    // cached work split of the answer kernel for the last (num_bits, shard rows) seen
+    uint32_t split_nb = 0, split_dmax = 0, split_dmin = 0, split_b = 0;
+    uint64_t split_first = 0, split_rows = 0;
     // optional per-launch timing of the dominant (fused) kernel, for bench.py's roofline
     bool timing = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pool;
@@ -322,6 +325,55 @@ Plan make_plan(uint32_t nb, uint64_t first_row, uint64_t n_rows, int num_sms, in
         }
     }
     return best;
+}
+
+// Work split of the answer kernel (answer_kernel.cu TaskIter): depth range [Dmin, Dmax] and breadth B.
+// Dmin is chosen by replaying every CTA's task sequence against a two-term cost model measured on B200
+// (a task costs its walk + breadth-first top, ~28k cycles, plus ~8k cycles per depth-first node of its threads).
+struct AnswerSplit {
+    uint32_t Dmax, Dmin, B;
+};
+AnswerSplit choose_answer_split(uint32_t nb, uint64_t first_row, uint64_t n_rows, int num_sms) {
+    AnswerSplit sp{};
+    sp.B = nb - 1 < (uint32_t)kFusedLogThreads ? nb - 1 : (uint32_t)kFusedLogThreads;
+    sp.Dmax = nb - 1 - sp.B < 7u ? nb - 1 - sp.B : 7u;
+    if (const char* e = getenv("PIRB_DFS_DEPTH")) {
+        const uint32_t f = (uint32_t)atoi(e);
+        if (f < sp.Dmax) sp.Dmax = f;
+    }
+    sp.Dmin = sp.Dmax;
+    if (const char* e = getenv("PIRB_DMIN")) {
+        const uint32_t f = (uint32_t)atoi(e);
+        sp.Dmin = f < sp.Dmax ? f : sp.Dmax;
+        return sp;
+    }
+    double best = -1.0;
+    for (uint32_t dmin = sp.Dmax + 1; dmin-- > 0;) {  // coarse to fine: a finer split must win by 0.5%
+        const uint64_t C = answer_chunks(first_row, n_rows, sp.B, dmin);
+        const uint64_t G = C < (uint64_t)num_sms ? C : (uint64_t)num_sms;
+        const uint64_t cf = first_row >> (sp.B + dmin + 1);
+        double worst = 0.0;
+        for (uint64_t b = 0; b < G; b++) {
+            uint64_t cur = cf + b * C / G, end = cf + (b + 1) * C / G;
+            double cost = 0.0;
+            while (cur < end) {
+                uint32_t d = dmin;
+                uint64_t span = 1;
+                while (d < sp.Dmax && !(cur & (2 * span - 1)) && cur + 2 * span <= end) {
+                    d++;
+                    span *= 2;
+                }
+                cost += 28000.0 + 8000.0 * (double)((2u << d) - 1u);
+                cur += span;
+            }
+            if (cost > worst) worst = cost;
+        }
+        if (best < 0.0 || worst < best * 0.995) {
+            best = worst;
+            sp.Dmin = dmin;
+        }
+    }
+    return sp;
 }
 }  // namespace
 
@@ -522,19 +574,32 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
     static const bool use_v1 = getenv("PIRB_KERNEL") && !strcmp(getenv("PIRB_KERNEL"), "v1");
     if (!use_v1 && answer_kernel_supports(g.row_bytes, 0)) {
         // warp-specialised kernel: walks the top of the tree itself, one launch per query
-        Plan p4 = make_plan(g.nb, g.first_row, g.n_rows, ctx.num_sms, 4);
+        if (db->split_nb != g.nb || db->split_first != g.first_row || db->split_rows != g.n_rows) {
+            const AnswerSplit sp = choose_answer_split(g.nb, g.first_row, g.n_rows, ctx.num_sms);
+            db->split_nb = g.nb;
+            db->split_first = g.first_row;
+            db->split_rows = g.n_rows;
+            db->split_dmax = sp.Dmax;
+            db->split_dmin = sp.Dmin;
+            db->split_b = sp.B;
+        }
         AnswerPlan ap{};
         ap.db = db->d_slots;
         ap.row_bytes = g.row_bytes;
         ap.first_row = g.first_row;
         ap.n_rows = g.n_rows;
-        ap.D = p4.D;
-        ap.B = p4.B;
-        ap.Fc = p4.Fc;
-        ap.task_first = p4.task_first;
-        ap.task_count = p4.task_count;
+        ap.D = db->split_dmax;
+        ap.B = db->split_b;
+        ap.Dmin = db->split_dmin;
         ap.out = (uint32_t*)d_out;
         if (const char* dbg = getenv("PIRB_DEBUG_FLAGS")) ap.pad = (uint32_t)atoi(dbg);  // timing experiments only
+        static const bool phase_debug = getenv("PIRB_PHASE_DEBUG") != nullptr;
+        unsigned long long* d_dbg = nullptr;
+        if (phase_debug) {
+            CU(cudaMalloc(&d_dbg, 8 * 8 * 1024));
+            CU(cudaMemsetAsync(d_dbg, 0, 8 * 8 * 1024, st));
+            ap.dbg = d_dbg;
+        }
         cudaEvent_t e0 = nullptr, e1 = nullptr;
         if (db->timing) {
             if (db->ev_used == db->ev_pool.size()) {
@@ -549,6 +614,23 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
         }
         CU(launch_answer(qc, ap, ctx.d_t0, ctx.smem_base, ctx.num_sms, st));
         if (e1) CU(cudaEventRecord(e1, st));
+        if (d_dbg) {  // development aid: average per-CTA cycles per phase of the tree warps, to stderr
+            std::vector<unsigned long long> h(8 * 1024);
+            CU(cudaStreamSynchronize(st));
+            CU(cudaMemcpy(h.data(), d_dbg, 8 * 8 * 1024, cudaMemcpyDeviceToHost));
+            cudaFree(d_dbg);
+            double sum[8] = {0}, mx = 0;
+            int n = 0;
+            for (int b = 0; b < 1024; b++) {
+                if (!h[8 * b + 5]) continue;
+                n++;
+                for (int k = 0; k < 8; k++) sum[k] += (double)h[8 * b + k];
+                if ((double)(h[8 * b + 5] + h[8 * b + 7]) > mx) mx = (double)(h[8 * b + 5] + h[8 * b + 7]);
+            }
+            if (n)
+                fprintf(stderr, "[phase] ctas %d tasks %.2f | prologue %.0f top %.0f bfs %.0f dfs %.0f (of which ring-full wait %.0f) tail %.0f | tree total %.0f cycles, slowest CTA %.0f\n",
+                        n, sum[6] / n, sum[7] / n, sum[0] / n, sum[1] / n, sum[3] / n, sum[2] / n, sum[4] / n, sum[5] / n, mx);
+        }
         return PIR_OK;
     }
     Plan p = make_plan(g.nb, g.first_row, g.n_rows, ctx.num_sms);
@@ -1248,4 +1330,9 @@ extern "C" int pir_server_answer_batch(pir_server* s, const pir_query* qs, uint3
 
 extern "C" int pir_server_answer(pir_server* s, const pir_query* q, void* out, size_t out_len) {
     return pir_server_answer_batch(s, q, 1, out, out_len);
+}
+extern "C" void pir_debug_answer_split(uint32_t nb, uint64_t first_row, uint64_t n_rows, int num_sms, uint32_t* Dmax,
+                                       uint32_t* Dmin, uint32_t* B) {
+    AnswerSplit sp = choose_answer_split(nb, first_row, n_rows, num_sms);
+    *Dmax = sp.Dmax; *Dmin = sp.Dmin; *B = sp.B;
 }

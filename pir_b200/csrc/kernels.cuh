@@ -37,10 +37,12 @@ struct AnswerPlan {
     uint64_t row_bytes;   // power of two, 16..512
     uint64_t first_row;
     uint64_t n_rows;
-    uint32_t D, B, Fc, pad;
-    uint64_t task_first;
-    uint64_t task_count;
-    uint32_t* out;        // row_bytes/4 words, zeroed before launch (atomic XOR)
+    uint32_t D;           // deepest per-thread DFS depth used (a thread owns up to 2^(D+1) rows)
+    uint32_t B;           // breadth-first levels per task: 2^B thread roots
+    uint32_t Dmin;        // chunk granularity of the CTA work split: chunks of 2^(B+Dmin+1) rows
+    uint32_t pad;         // debug flags
+    uint32_t* out;        // row_bytes/4 words, XOR-accumulated (atomics); the caller zeroes
+    unsigned long long* dbg;  // optional per-CTA phase cycle counters (PIRB_PHASE_DEBUG), else null
 };
 
 struct TopPlan {
@@ -78,6 +80,7 @@ cudaError_t configure_kernels();
 // warp-specialised fused expand+scan kernel (answer_kernel.cu)
 bool answer_kernel_supports(uint64_t row_bytes, uint32_t D);
 cudaError_t configure_answer_kernel();
+uint64_t answer_chunks(uint64_t first_row, uint64_t n_rows, uint32_t B, uint32_t Dmin);
 cudaError_t launch_answer(const QueryConst& qc, const AnswerPlan& ap, const uint32_t* d_t0, uint32_t smem_base,
                           int num_sms, cudaStream_t st);
 
