@@ -26,6 +26,7 @@ sys.path.insert(0, ROOT)
 
 LOG_ROWS = int(os.environ.get("PIRB_BENCH_LOG_ROWS", "24"))
 SLOT_BYTES = int(os.environ.get("PIRB_BENCH_SLOT_BYTES", "256"))
+QUERIES = int(os.environ.get("PIRB_BENCH_QUERIES", "1"))   # queries answered per step (one pir_answer_batch call)
 SEED = 2024
 CPU_SAMPLE_LOG_ROWS = 20
 METRIC = "dpf_pir_answer_db_scan_throughput"
@@ -33,8 +34,9 @@ UNIT = "GB/s"
 
 
 def workload_name():
-    return "2^%d rows x %d-byte slots (%.1f GiB DB), single query, group size 1" % (
-        LOG_ROWS, SLOT_BYTES, (1 << LOG_ROWS) * SLOT_BYTES / 2**30)
+    return "2^%d rows x %d-byte slots (%.1f GiB DB), %s, group size 1" % (
+        LOG_ROWS, SLOT_BYTES, (1 << LOG_ROWS) * SLOT_BYTES / 2**30,
+        "single query" if QUERIES == 1 else "batch of %d queries per step" % QUERIES)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -45,7 +47,7 @@ def cpu_reference_run(steps, warmup):
     import oracle
     cores = len(os.sched_getaffinity(0))
     n = 1 << LOG_ROWS
-    rows = min(n, 1 << CPU_SAMPLE_LOG_ROWS)
+    rows = min(n, 1 << CPU_SAMPLE_LOG_ROWS, (256 << 20) // SLOT_BYTES)   # at most 256 MiB of slots
     nb = oracle.num_bits_for(n, 1, False)
     data = oracle.synth_fill(SEED, 0, rows, SLOT_BYTES)
     times = []
@@ -59,8 +61,8 @@ def cpu_reference_run(steps, warmup):
             times.append(dt)
     ms = 1e3 * sum(times) / len(times)
     gbs = rows * SLOT_BYTES / (ms * 1e-3) / 1e9
-    sample = "first 2^%d of 2^%d rows (%d MiB), %d-level per-row Evaluate2P + serial XOR, per step" % (
-        CPU_SAMPLE_LOG_ROWS, LOG_ROWS, rows * SLOT_BYTES >> 20, nb)
+    sample = "first %d of 2^%d rows (%d MiB), %d-level per-row Evaluate2P + serial XOR, per step" % (
+        rows, LOG_ROWS, rows * SLOT_BYTES >> 20, nb)
     return gbs, ms, cores, sample
 
 
@@ -76,7 +78,7 @@ def reference_arm(args):
         "config": {"workload": workload_name()},
         "cpu_baseline": {"value": gbs, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": gbs, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "queries_per_s": 1e3 / (ms * (1 << LOG_ROWS) / min(1 << LOG_ROWS, 1 << CPU_SAMPLE_LOG_ROWS)),
+        "queries_per_s": gbs * 1e9 / ((1 << LOG_ROWS) * SLOT_BYTES),
         "note": "Go toolchain absent: C restatement of the reference algorithm (oracle/), conservative (no Go allocs/goroutines)",
     }
     print(json.dumps(line), flush=True)
@@ -172,8 +174,17 @@ def gpu_arm(args):
         tape = (C.c_uint8 * 97).from_buffer_copy(rng.integers(0, 256, size=97, dtype=np.uint8).tobytes())
         _capi.check(L.pir_client_gen_two_server(nb, idx, 1, tape, C.byref(qs[2 * i]), C.byref(qs[2 * i + 1])))
 
+    if QUERIES > 1 and world > 1:
+        raise SystemExit("bench.py: PIRB_BENCH_QUERIES > 1 is a single-GPU workload (configs[3])")
+    qbatch = None
+    if QUERIES > 1:
+        qbatch = (_capi.PirQuery * QUERIES)()
+        scratch = _capi.PirQuery()
+        for k in range(QUERIES):
+            tape = (C.c_uint8 * 97).from_buffer_copy(rng.integers(0, 256, size=97, dtype=np.uint8).tobytes())
+            _capi.check(L.pir_client_gen_two_server(nb, int(rng.integers(0, n)), 1, tape, C.byref(qbatch[k]), C.byref(scratch)))
     stream = torch.cuda.Stream()
-    d_out = torch.zeros(S, dtype=torch.uint8, device="cuda")
+    d_out = torch.zeros(S * QUERIES, dtype=torch.uint8, device="cuda")
     sp = C.c_void_p(stream.cuda_stream)
     comb = None
     if world > 1:
@@ -186,6 +197,8 @@ def gpu_arm(args):
         """one query, database resident; N > 1: every rank's kernel accumulates into ring slot `slot` on rank 0"""
         if world > 1:
             comb.accumulate(h, qs[2 * i], i if slot is None else slot, sp)
+        elif qbatch is not None:
+            _capi.check(L.pir_answer_batch_device(h, qbatch, QUERIES, C.c_void_p(d_out.data_ptr()), sp))
         else:
             _capi.check(L.pir_answer_batch_device(h, C.byref(qs[2 * i]), 1, C.c_void_p(d_out.data_ptr()), sp))
 
@@ -203,7 +216,7 @@ def gpu_arm(args):
         for share in (0, 1):
             _capi.check(L.pir_answer_batch_device(h, C.byref(qs[2 * i + share]), 1, C.c_void_p(d_out.data_ptr()), sp))
             stream.synchronize()
-            acc ^= d_out
+            acc ^= d_out[:S]
         recovered = acc.cpu().numpy()
     else:
         for share in (0, 1):
@@ -248,15 +261,22 @@ def gpu_arm(args):
     _capi.check(L.pir_db_set_kernel_timing(h, 0))
 
     # ---- end-to-end timed region: host key in, host answer out, every step ----
-    out_host = np.zeros(S, dtype=np.uint8)
-    e2e_ok = True
+    out_host = np.zeros(S * QUERIES, dtype=np.uint8)
     if world == 1:
         for i in range(min(3, args.warmup)):
-            _capi.check(L.pir_answer(h, C.byref(qs[2 * i]), out_host.ctypes.data_as(C.c_void_p), S))
+            if qbatch is not None:
+                _capi.check(L.pir_answer_batch(h, qbatch, QUERIES, out_host.ctypes.data_as(C.c_void_p), S * QUERIES))
+            else:
+                _capi.check(L.pir_answer(h, C.byref(qs[2 * i]), out_host.ctypes.data_as(C.c_void_p), S))
     barrier()
     t0 = time.perf_counter()
     for i in range(args.warmup, total):
-        if world == 1:
+        if qbatch is not None:
+            tq = time.perf_counter()
+            _capi.check(L.pir_answer_batch(h, qbatch, QUERIES, out_host.ctypes.data_as(C.c_void_p), S * QUERIES))
+            if os.environ.get("PIRB_BENCH_VERBOSE"):
+                print("e2e batch call %.2f ms" % ((time.perf_counter() - tq) * 1e3), file=sys.stderr)
+        elif world == 1:
             _capi.check(L.pir_answer(h, C.byref(qs[2 * i]), out_host.ctypes.data_as(C.c_void_p), S))
         else:
             # every rank: host key -> its shard's kernel -> XOR into ring slot on rank 0;
@@ -276,7 +296,7 @@ def gpu_arm(args):
         k_avg_ms = kms.value / max(1, kcount.value)
 
     if rank == 0:
-        db_bytes = n * S
+        db_bytes = n * S * QUERIES   # a batch makes one pass over the database per query
         ms_step = dev_ms / args.steps
         value = db_bytes / (ms_step * 1e-3) / 1e9
         e2e_step = e2e_ms / args.steps
@@ -304,10 +324,11 @@ def gpu_arm(args):
                        "combine": "none" if world == 1 else "every shard's kernel XORs its %d-byte partial into rank 0's ring slot "
                                   "(red.global.xor over a CUDA IPC mapping / NVLink); no NCCL in the data path" % S,
                        "queries": "distinct seeded key per step, share 0"},
-            "queries_per_s": 1e3 / ms_step,
+            "queries_per_s": 1e3 * QUERIES / ms_step,
             "e2e": {"value": db_bytes / (e2e_step * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": e2e_step,
-                    "h2d_bytes_per_step": C.sizeof(_capi.PirQuery), "d2h_bytes_per_step": S,
-                    "api": "pir_answer (C ABI, host key in / host answer out, stream sync per query)" if world == 1 else
+                    "h2d_bytes_per_step": C.sizeof(_capi.PirQuery) * QUERIES, "d2h_bytes_per_step": S * QUERIES,
+                    "api": ("pir_answer (C ABI, host key in / host answer out, stream sync per query)" if QUERIES == 1 else
+                            "pir_answer_batch (C ABI, host keys in / host answers out, one sync per batch)") if world == 1 else
                            "pir_answer_accumulate_device on every rank + pir_combine_wait_read on rank 0 (host key in, combined host answer out)"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,

@@ -44,15 +44,19 @@ constexpr uint32_t kOffBfsS = 0;                                    // [2][512] 
 constexpr uint32_t kOffBfsT = 16384;                                // [2][512] u8       =  1 KB
 constexpr uint32_t kOffPathS = kV2MaxDepth * 4 * kTreeThreads * 4;  // [65] uint4
 constexpr uint32_t kOffPathT = kOffPathS + 65 * 16;                 // [65] u32
-constexpr uint32_t kOffRed = kOffPathT + 65 * 4 + 12;               // [128] u32
-constexpr uint32_t kOffTasks = kOffRed + 512;                       // [1 + kMaxTasks] u32
+constexpr uint32_t kOffTasks = kOffPathT + 65 * 4 + 12;             // [1 + kMaxTasks] u32
 constexpr uint32_t kScratchEnd = kOffTasks + 4 + 4 * kMaxTasks;
 // above the tables (absolute shared-window addresses)
 constexpr uint32_t kAbsLists = kTableEnd;                                      // [20 warps][256] u16
 constexpr uint32_t kAbsRing = kAbsLists + (kAnswerThreads / 32) * kListEntries * 2;  // [kRing][512] u32
 constexpr uint32_t kAbsBars = kAbsRing + kRing * kTreeThreads * 4;             // full[kRing], empty[kRing] u64
 constexpr uint32_t kAbsClaim = kAbsBars + 2 * kRing * 8;                       // claim counter, done[kRing] u32
-constexpr uint32_t kSmemEnd = kAbsClaim + 4 * (1 + kRing) + 12;
+constexpr uint32_t kAbsRed = kAbsClaim + 4 * (1 + kRing) + 12;                 // [kMaxRowBytes / 4] u32: the CTA's partial answer
+constexpr uint32_t kMaxRowBytes = 4096;                                        // rows of 16..4096 bytes (power of two)
+constexpr uint32_t kSmemEnd = kAbsRed + kMaxRowBytes;
+__device__ __forceinline__ uint32_t* red_words() {
+    return reinterpret_cast<uint32_t*>(g_smem2 + (kAbsRed - smem_addr(g_smem2)));
+}
 
 enum : int { BAR_TREE = 1 };
 
@@ -111,7 +115,8 @@ struct ScanLane {
 __device__ __forceinline__ ScanLane scan_lane(const AnswerPlan& ap) {
     ScanLane sl;
     const uint32_t lane = threadIdx.x & 31u;
-    sl.c = (uint32_t)(ap.row_bytes >> 4);  // 16-byte chunks per row, power of two <= 32
+    sl.c = (uint32_t)(ap.row_bytes >> 4);  // 16-byte chunks per row (power of two); rows wider than a warp
+    if (sl.c > 32u) sl.c = 32u;            // load (512 B) are fetched in NCB column blocks of 512 B
     const uint32_t logc = 31u - __clz(sl.c);
     sl.rpl = 32u >> logc;                  // rows per warp load
     sl.h = lane >> logc;
@@ -123,10 +128,10 @@ __device__ __forceinline__ ScanLane scan_lane(const AnswerPlan& ap) {
 // holds thread i's selection bits for its rows [slice_off, slice_off + 2^slice_log) of the task
 // (thread i owns task rows [i << rows_log, (i+1) << rows_log)).  `list` is a private 512-byte scratch of
 // the calling warp.
-template <int UNROLL>
+template <int UNROLL, int NCB>
 __device__ __forceinline__ void scan_group(const AnswerPlan& ap, const ScanLane& sl, const uint32_t* wbuf,
                                            uint32_t g, int64_t task_row0, uint32_t rows_log, uint32_t slice_off,
-                                           uint16_t* list, uint4& acc) {
+                                           uint16_t* list, uint4 (&acc)[NCB]) {
     const uint32_t lane = threadIdx.x & 31u;
     uint32_t w = wbuf[g * 32u + lane];
     const uint32_t cnt = __popc(w);
@@ -141,45 +146,67 @@ __device__ __forceinline__ void scan_group(const AnswerPlan& ap, const ScanLane&
     // byte address of the group's first row, for this lane's 16-byte chunk (rows before the shard's
     // first row are never selected, so a negative offset is never dereferenced)
     const uint8_t* gbase = sl.lane_db + (task_row0 + ((int64_t)(g * 32u) << rows_log)) * (int64_t)ap.row_bytes;
+    // The list is kept as rpl interleaved sub-lists (entry p goes to sub-list p % rpl, the lane group that
+    // will fetch it), so a lane group reads its next 8 row numbers with ONE 128-bit shared load.
     uint32_t pos = pre - cnt;
     const uint32_t rbase = (lane << rows_log) + slice_off;
+    const uint32_t lrpl = 31u - __clz(sl.rpl), sub_stride = kListEntries >> lrpl;
     while (w) {
-        list[pos++] = (uint16_t)(rbase + (uint32_t)__ffs(w) - 1u);
+        list[(pos & (sl.rpl - 1u)) * sub_stride + (pos >> lrpl)] = (uint16_t)(rbase + (uint32_t)__ffs(w) - 1u);
+        pos++;
         w &= w - 1u;
     }
     __syncwarp();
-    for (uint32_t e0 = 0; e0 < ((ap.pad & 1u) ? 0u : total); e0 += sl.rpl * UNROLL) {
-        uint4 v[UNROLL];
+    const uint16_t* sub = list + sl.h * sub_stride;
 #pragma unroll
-        for (int u = 0; u < UNROLL; u++) {
-            const uint32_t e = e0 + u * sl.rpl + sl.h;
-            v[u] = make_uint4(0, 0, 0, 0);
-            if (e < total) v[u] = ldg_nc_v4(gbase + (uint64_t)list[e] * ap.row_bytes);
-        }
+    for (int cb = 0; cb < NCB; cb++) {
+        const uint8_t* cbase = gbase + cb * 512;
+        for (uint32_t e0 = 0; e0 < ((ap.pad & 1u) ? 0u : total); e0 += sl.rpl * UNROLL) {
+            uint4 v[UNROLL];
 #pragma unroll
-        for (int u = 0; u < UNROLL; u += 2) {
-            acc.x ^= v[u].x ^ v[u + 1].x; acc.y ^= v[u].y ^ v[u + 1].y;
-            acc.z ^= v[u].z ^ v[u + 1].z; acc.w ^= v[u].w ^ v[u + 1].w;
+            for (int k = 0; k < UNROLL / 8; k++) {
+                const uint32_t eb = e0 + (uint32_t)k * 8u * sl.rpl;  // first entry of this block of 8 loads
+                uint4 L = make_uint4(0, 0, 0, 0);
+                if (eb < total) L = *reinterpret_cast<const uint4*>(sub + (eb >> lrpl));
+                const uint32_t lw[4] = {L.x, L.y, L.z, L.w};
+#pragma unroll
+                for (int u = 0; u < 8; u++) {
+                    const uint32_t e = eb + (uint32_t)u * sl.rpl + sl.h;
+                    const uint32_t row = (lw[u >> 1] >> ((u & 1) * 16)) & 0xffffu;
+                    v[k * 8 + u] = make_uint4(0, 0, 0, 0);
+                    if (e < total) v[k * 8 + u] = ldg_nc_v4(cbase + (uint64_t)row * ap.row_bytes);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < UNROLL; u += 2) {
+                acc[cb].x ^= v[u].x ^ v[u + 1].x; acc[cb].y ^= v[u].y ^ v[u + 1].y;
+                acc[cb].z ^= v[u].z ^ v[u + 1].z; acc[cb].w ^= v[u].w ^ v[u + 1].w;
+            }
         }
     }
     __syncwarp();
 }
 
 // fold the sub-rows of a warp load, then XOR into the CTA's shared accumulator
-__device__ __forceinline__ void fold_acc(const ScanLane& sl, uint4 acc) {
+template <int NCB>
+__device__ __forceinline__ void fold_acc(const ScanLane& sl, uint4 (&accs)[NCB]) {
     const uint32_t lane = threadIdx.x & 31u;
-    for (uint32_t off = 16; off >= sl.c && off > 0; off >>= 1) {
-        acc.x ^= __shfl_xor_sync(0xffffffffu, acc.x, off);
-        acc.y ^= __shfl_xor_sync(0xffffffffu, acc.y, off);
-        acc.z ^= __shfl_xor_sync(0xffffffffu, acc.z, off);
-        acc.w ^= __shfl_xor_sync(0xffffffffu, acc.w, off);
-    }
-    uint32_t* red = reinterpret_cast<uint32_t*>(g_smem2 + kOffRed);
-    if (lane < sl.c && (acc.x | acc.y | acc.z | acc.w)) {
-        atomicXor(&red[lane * 4 + 0], acc.x);
-        atomicXor(&red[lane * 4 + 1], acc.y);
-        atomicXor(&red[lane * 4 + 2], acc.z);
-        atomicXor(&red[lane * 4 + 3], acc.w);
+    uint32_t* red = red_words();
+#pragma unroll
+    for (int cb = 0; cb < NCB; cb++) {
+        uint4 acc = accs[cb];
+        for (uint32_t off = 16; off >= sl.c && off > 0; off >>= 1) {
+            acc.x ^= __shfl_xor_sync(0xffffffffu, acc.x, off);
+            acc.y ^= __shfl_xor_sync(0xffffffffu, acc.y, off);
+            acc.z ^= __shfl_xor_sync(0xffffffffu, acc.z, off);
+            acc.w ^= __shfl_xor_sync(0xffffffffu, acc.w, off);
+        }
+        if (lane < sl.c && (acc.x | acc.y | acc.z | acc.w)) {
+            atomicXor(&red[cb * 128 + lane * 4 + 0], acc.x);
+            atomicXor(&red[cb * 128 + lane * 4 + 1], acc.y);
+            atomicXor(&red[cb * 128 + lane * 4 + 2], acc.z);
+            atomicXor(&red[cb * 128 + lane * 4 + 3], acc.w);
+        }
     }
 }
 
@@ -290,6 +317,7 @@ constexpr uint32_t kCoopMaxLevel = 6;  // breadth-first levels with <= 64 nodes 
 // Work unit = one 32-word group of one slice, claimed in order from a shared counter, so the backlog at
 // the end of the kernel is drained by all 20 warps.  The warp that completes a slice's last group hands
 // the ring slot back to the tree warps.
+template <int NCB>
 __device__ __forceinline__ void consume_slices(const AnswerPlan& ap, uint32_t warp_in_cta) {
     const uint32_t lane = threadIdx.x & 31u;
     const ScanLane sl = scan_lane(ap);
@@ -302,7 +330,9 @@ __device__ __forceinline__ void consume_slices(const AnswerPlan& ap, uint32_t wa
     uint64_t row_start = 0;
     uint32_t D = 0;
     uint32_t gs0 = 0, gs1 = 0;  // global slice range of the current task
-    uint4 acc = make_uint4(0, 0, 0, 0);
+    uint4 acc[NCB];
+#pragma unroll
+    for (int cb = 0; cb < NCB; cb++) acc[cb] = make_uint4(0, 0, 0, 0);
     while (true) {
         uint32_t u = 0;
         if (lane == 0) u = atomicAdd(claim, 1u);
@@ -321,7 +351,7 @@ __device__ __forceinline__ void consume_slices(const AnswerPlan& ap, uint32_t wa
         const uint32_t slot = gsl & (kRing - 1u), par = (gsl / kRing) & 1u;
         mbar_wait(full_bar(slot), par);
         const uint32_t slog = slice_log(D);
-        scan_group<16>(ap, sl, ring_words(slot), g, (int64_t)row_start - (int64_t)ap.first_row, D + 1u,
+        scan_group<(NCB >= 4 ? 8 : 16), NCB>(ap, sl, ring_words(slot), g, (int64_t)row_start - (int64_t)ap.first_row, D + 1u,
                        (gsl - gs0) << slog, list, acc);
         __syncwarp();
         if (lane == 0) {
@@ -332,10 +362,11 @@ __device__ __forceinline__ void consume_slices(const AnswerPlan& ap, uint32_t wa
             }
         }
     }
-    fold_acc(sl, acc);
+    fold_acc<NCB>(sl, acc);
 }
 
 // ---- tree role ------------------------------------------------------------------------------------
+template <int NCB>
 __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan& ap, uint32_t lc, long long c_entry) {
     const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31u;
     const uint32_t B = ap.B;
@@ -494,7 +525,7 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
         it++;
     }
     // nothing left to expand: help the scan warps drain the ring
-    consume_slices(ap, warp);
+    consume_slices<NCB>(ap, warp);
     PHASE(c_tail)
 #undef PHASE
     if (ap.dbg && tid == 0) {
@@ -505,6 +536,7 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
     }
 }
 
+template <int NCB>
 __global__ void __launch_bounds__(kAnswerThreads, 1)
 answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ AnswerPlan ap,
               const uint32_t* __restrict__ t0) {
@@ -516,8 +548,9 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
         if (base + dyn < kSmemEnd || base + kScratchEnd > kTableBase) __trap();
     }
     fill_tables(t0);
-    uint32_t* red = reinterpret_cast<uint32_t*>(g_smem2 + kOffRed);
-    if (threadIdx.x < 128) red[threadIdx.x] = 0;
+    uint32_t* red = red_words();
+    const uint32_t words_out = (uint32_t)(ap.row_bytes >> 2);
+    for (uint32_t i = threadIdx.x; i < words_out; i += kAnswerThreads) red[i] = 0;
     if (threadIdx.x == kAnswerThreads - 1) build_task_list(ap, reinterpret_cast<uint32_t*>(g_smem2 + kOffTasks));
     if (threadIdx.x == kAnswerThreads - 2) {
         for (uint32_t k = 0; k < kRing; k++) {
@@ -529,24 +562,27 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
     }
     __syncthreads();
     if (threadIdx.x < kTreeThreads)
-        tree_role(qc, ap, lane_const(), c_entry);
+        tree_role<NCB>(qc, ap, lane_const(), c_entry);
     else
-        consume_slices(ap, threadIdx.x >> 5);
+        consume_slices<NCB>(ap, threadIdx.x >> 5);
     __syncthreads();
-    const uint32_t words_out = (uint32_t)(ap.row_bytes >> 2);
-    if (threadIdx.x < words_out) {
-        const uint32_t v = red[threadIdx.x];
-        if (v) atomicXor(&ap.out[threadIdx.x], v);
+    for (uint32_t i = threadIdx.x; i < words_out; i += kAnswerThreads) {
+        const uint32_t v = red[i];
+        if (v) atomicXor(&ap.out[i], v);
     }
 }
 
 bool answer_kernel_supports(uint64_t row_bytes, uint32_t D) {
-    if (row_bytes < 16 || row_bytes > 512 || (row_bytes & (row_bytes - 1))) return false;
+    if (row_bytes < 16 || row_bytes > kMaxRowBytes || (row_bytes & (row_bytes - 1))) return false;
     return D <= (uint32_t)kV2MaxDepth;
 }
 
 cudaError_t configure_answer_kernel() {
-    return cudaFuncSetAttribute(answer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemEnd);
+    cudaError_t e = cudaFuncSetAttribute(answer_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemEnd);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(answer_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemEnd);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(answer_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemEnd);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(answer_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemEnd);
+    return e;
 }
 
 uint64_t answer_chunks(uint64_t first_row, uint64_t n_rows, uint32_t B, uint32_t Dmin) {
@@ -563,7 +599,15 @@ cudaError_t launch_answer(const QueryConst& qc, const AnswerPlan& ap, const uint
     // more CTAs than SMs (in waves) rather than overflow it
     const uint64_t gmin = (chunks + (kMaxTasks - 1)) / kMaxTasks;
     if (g < gmin) g = gmin;
-    answer_kernel<<<(unsigned)g, kAnswerThreads, kSmemEnd - smem_base, st>>>(qc, ap, d_t0);
+    const size_t smem = kSmemEnd - smem_base;
+    if (ap.row_bytes <= 512)
+        answer_kernel<1><<<(unsigned)g, kAnswerThreads, smem, st>>>(qc, ap, d_t0);
+    else if (ap.row_bytes == 1024)
+        answer_kernel<2><<<(unsigned)g, kAnswerThreads, smem, st>>>(qc, ap, d_t0);
+    else if (ap.row_bytes == 2048)
+        answer_kernel<4><<<(unsigned)g, kAnswerThreads, smem, st>>>(qc, ap, d_t0);
+    else
+        answer_kernel<8><<<(unsigned)g, kAnswerThreads, smem, st>>>(qc, ap, d_t0);
     count_launch();
     return cudaGetLastError();
 }

@@ -627,6 +627,11 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
                 for (int k = 0; k < 8; k++) sum[k] += (double)h[8 * b + k];
                 if ((double)(h[8 * b + 5] + h[8 * b + 7]) > mx) mx = (double)(h[8 * b + 5] + h[8 * b + 7]);
             }
+            if (getenv("PIRB_PHASE_DEBUG")[0] == '2')
+                for (int b = 0; b < 1024; b++)
+                    if (h[8 * b + 5])
+                        fprintf(stderr, "[cta %d] tasks %llu prologue %llu top %llu bfs %llu dfs %llu tail %llu total %llu\n", b, h[8 * b + 6],
+                                h[8 * b + 7], h[8 * b + 0], h[8 * b + 1], h[8 * b + 3], h[8 * b + 4], h[8 * b + 5] + h[8 * b + 7]);
             if (n)
                 fprintf(stderr, "[phase] ctas %d tasks %.2f | prologue %.0f top %.0f bfs %.0f dfs %.0f (of which ring-full wait %.0f) tail %.0f | tree total %.0f cycles, slowest CTA %.0f\n",
                         n, sum[6] / n, sum[7] / n, sum[0] / n, sum[1] / n, sum[3] / n, sum[2] / n, sum[4] / n, sum[5] / n, mx);

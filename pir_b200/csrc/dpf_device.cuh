@@ -58,13 +58,15 @@ __device__ __forceinline__ uint32_t lane_const() {
 // Fill the lane-replicated tables.  t0 points at the 256-word base table T0 (global/constant).
 // All threads of the CTA call this; the caller __syncthreads() afterwards.
 __device__ __forceinline__ void fill_tables(const uint32_t* __restrict__ t0) {
-    // word index w in [0, 32768): pair = w >> 14, x = (w >> 6) & 255, half = (w >> 5) & 1, lane = w & 31
-    for (uint32_t w = threadIdx.x; w < 32768u; w += blockDim.x) {
+    // word index w in [0, 32768): pair = w >> 14, x = (w >> 6) & 255, half = (w >> 5) & 1, lane = w & 31;
+    // four consecutive words hold the same value, so every thread stores 16 bytes at a time
+    for (uint32_t q = threadIdx.x; q < 8192u; q += blockDim.x) {
+        const uint32_t w = q * 4u;
         uint32_t pair = w >> 14, x = (w >> 6) & 255u, half = (w >> 5) & 1u;
         uint32_t v = t0[x];
         uint32_t rot = (pair * 2u + half) * 8u;  // T1 = rotl(T0,8), T2 = rotl(T0,16), T3 = rotl(T0,24)
         v = __funnelshift_l(v, v, rot);
-        asm volatile("st.shared.u32 [%0], %1;" ::"r"(kTableBase + w * 4u), "r"(v) : "memory");
+        asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(kTableBase + w * 4u), "r"(v) : "memory");
     }
 }
 

@@ -1,6 +1,6 @@
 #!/bin/bash
 # per-phase cycle counters of the answer kernel's tree warps (development aid)
-export PIRB_PHASE_DEBUG=1
+export PIRB_PHASE_DEBUG=${PIRB_PHASE_DEBUG:-1}
 python - <<'PY'
 import ctypes as C, os, sys
 import numpy as np
