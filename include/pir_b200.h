@@ -13,6 +13,7 @@
  *   Database{Slots []*Slot}                   db.go:22-26           -> pir_db handle (flat device copy)
  *   Database.SetKeywords                      db.go:392-394         -> pir_db_set_keywords
  *   QueryShare + dpf.Key2P + dpf.PrfKey       query.go:14-22, dpf/common.go:13-35 -> pir_query POD
+ *   GenerateAuditForSharedQuery(WithExpandedBits) aspir.go:246-283   -> pir_audit_shared_query(_with_bits)
  *
  * Conventions
  *   - every function returns PIR_OK (0) or a negative pir_status; pir_last_error() gives a
@@ -180,6 +181,21 @@ int pir_combine_wait_read(pir_combine* c, uint32_t slot, uint32_t expected, void
                           uint32_t timeout_ms);
 /* Device address of a slot in this process (for device-resident consumers / tests). */
 void* pir_combine_slot_ptr(pir_combine* c, uint32_t slot);
+
+/* ---- secret-shared ASPIR audit (aspir.go:227-295) ------------------------------ */
+/*
+ * GenerateAuditForSharedQuery (aspir.go:246-257): the key database is queried with group size 1 whatever
+ * the query says (aspir.go:251-254), and the server's auth-token share is XORed into the result
+ * (aspir.go:279-281, XorSlots semantics: min of the two lengths).  out receives slot_bytes bytes = the
+ * AuditTokenShare.  Like the reference (aspir.go:275-277 after db.go:79-89), a query whose own group size
+ * is not 1 is rejected with PIR_ERR_BAD_ARG ("Invalid challenge ciphertext result").
+ */
+int pir_audit_shared_query(pir_db* key_db, const pir_query* q, const void* auth_token, size_t token_len,
+                           void* out, size_t out_len);
+/* GenerateAuditForSharedQueryWithExpandedBits (aspir.go:261-283): the bits of ONE expansion can serve
+ * the data database and the key database. */
+int pir_audit_shared_query_with_bits(pir_db* key_db, uint32_t group_size, const uint8_t* bits, uint64_t n_rows,
+                                     const void* auth_token, size_t token_len, void* out, size_t out_len);
 
 /* ---- dpf package surface ---------------------------------------------------------------------- */
 /* (*Dpf).Evaluate2P (dpf/server.go:55-101) on n points: out[i] = Evaluate2P(share_number, key, xs[i])

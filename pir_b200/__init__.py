@@ -6,3 +6,4 @@ mirror of the reference's Go API for this path: `pir_b200.pir` (db.go / slot.go 
 """
 from . import _capi  # noqa: F401
 from . import dpf, pir  # noqa: F401
+from . import aspir  # noqa: F401,E402

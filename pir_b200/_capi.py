@@ -35,6 +35,7 @@ EXPORTS = [
     "pir_server_upload", "pir_server_fill_synthetic", "pir_server_answer", "pir_server_answer_batch",
     "pir_combine_create", "pir_combine_export", "pir_combine_open", "pir_combine_destroy",
     "pir_combine_reset", "pir_answer_accumulate_device", "pir_combine_wait_read", "pir_combine_slot_ptr",
+    "pir_audit_shared_query", "pir_audit_shared_query_with_bits",
 ]
 PIR_IPC_HANDLE_BYTES = 64
 
@@ -143,6 +144,8 @@ def lib():
     L.pir_combine_wait_read.argtypes = [vp, C.c_uint32, C.c_uint32, vp, C.c_size_t, C.c_uint32]
     L.pir_combine_slot_ptr.argtypes = [vp, C.c_uint32]
     L.pir_combine_slot_ptr.restype = vp
+    L.pir_audit_shared_query.argtypes = [vp, qp, vp, C.c_size_t, vp, C.c_size_t]
+    L.pir_audit_shared_query_with_bits.argtypes = [vp, C.c_uint32, u8p, C.c_uint64, vp, C.c_size_t, vp, C.c_size_t]
     L.pir_debug_round_keys.argtypes = [u8p, C.POINTER(C.c_uint32)]
     L.pir_debug_t0.argtypes = [C.POINTER(C.c_uint32)]
     if L.pir_abi_version() != 1:

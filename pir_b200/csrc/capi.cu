@@ -966,6 +966,34 @@ extern "C" void pir_debug_plan(uint32_t nb, uint64_t first_row, uint64_t n_rows,
     *D = p.D; *B = p.B; *Fc = p.Fc; *task_first = p.task_first; *task_count = p.task_count;
 }
 
+// ---- secret-shared ASPIR audit (aspir.go:227-295) -------------------------------------------------
+extern "C" int pir_audit_shared_query(pir_db* key_db, const pir_query* q, const void* auth_token, size_t token_len,
+                                      void* out, size_t out_len) {
+    if (!key_db || !q || (!auth_token && token_len) || !out) return fail(PIR_ERR_BAD_ARG, "null argument");
+    if (q->group_size != 1)  // aspir.go:275-277: len(res.Shares) = query.GroupSize must be 1
+        return fail(PIR_ERR_BAD_ARG, "Invalid challenge ciphertext result (query group size %u, the key database has 1)",
+                    q->group_size);
+    if (out_len < key_db->slot_bytes) return fail(PIR_ERR_BAD_ARG, "out_len %zu < %u", out_len, key_db->slot_bytes);
+    int rc = pir_answer(key_db, q, out, out_len);
+    if (rc) return rc;
+    const size_t n = token_len < key_db->slot_bytes ? token_len : key_db->slot_bytes;
+    pir_xor_combine(out, auth_token, n);
+    return PIR_OK;
+}
+
+extern "C" int pir_audit_shared_query_with_bits(pir_db* key_db, uint32_t group_size, const uint8_t* bits, uint64_t n_rows,
+                                                const void* auth_token, size_t token_len, void* out, size_t out_len) {
+    if (!key_db || (!auth_token && token_len) || !out) return fail(PIR_ERR_BAD_ARG, "null argument");
+    if (group_size != 1)
+        return fail(PIR_ERR_BAD_ARG, "Invalid challenge ciphertext result (query group size %u, the key database has 1)",
+                    group_size);
+    int rc = pir_answer_with_bits(key_db, 1, bits, n_rows, out, out_len);
+    if (rc) return rc;
+    const size_t n = token_len < key_db->slot_bytes ? token_len : key_db->slot_bytes;
+    pir_xor_combine(out, auth_token, n);
+    return PIR_OK;
+}
+
 // ---- multi-GPU combine ------------------------------------------------------------
 // Layout of a combine buffer on the owner GPU: [n_slots x slot_stride answer bytes][n_slots x u32 arrivals]
 // [u32 timeout flag].  slot_stride is a multiple of 16.

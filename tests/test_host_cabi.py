@@ -129,3 +129,33 @@ def test_product_never_imports_oracle():
                 src = open(os.path.join(dirpath, f)).read()
                 assert "import oracle" not in src and "from oracle" not in src, f
                 assert "pir_oracle" not in src and "orc_" not in src, f
+
+
+def test_auth_token_shares_xor_to_key_and_check_audit():
+    """aspir.go:227-243, 286-299 (host arithmetic, no device)."""
+    from pir_b200 import aspir, pir
+    key = pir.NewRandomSlot(16)
+    for n in (2, 3, 5):
+        shares = aspir.NewAuthTokenSharesForKey(key, n)
+        acc = pir.NewEmptySlot(16)
+        for s in shares:
+            pir.XorSlots(acc, s.T)
+        assert acc.Equal(key)
+    a, b = pir.NewRandomSlot(16), pir.NewRandomSlot(16)
+    assert aspir.CheckAudit(aspir.AuditTokenShare(a), aspir.AuditTokenShare(pir.Slot(bytes(a.Data))))
+    assert not aspir.CheckAudit(aspir.AuditTokenShare(a), aspir.AuditTokenShare(b))
+
+
+def test_multi_gpu_entry_points_fail_loudly_without_device():
+    L = _capi.lib()
+    if L.pir_device_count() > 0:
+        pytest.skip("a CUDA device is visible")
+    h = C.c_void_p()
+    devs = (C.c_int * 2)(0, 1)
+    assert L.pir_server_create(devs, 2, 1024, 32, 1, C.byref(h)) == _capi.PIR_ERR_CUDA
+    assert b"no CUDA device" in L.pir_last_error()
+    assert L.pir_combine_create(0, 4, 256, C.byref(h)) == _capi.PIR_ERR_CUDA
+    # argument validation happens before any device work
+    assert L.pir_combine_create(0, 0, 256, C.byref(h)) == _capi.PIR_ERR_BAD_ARG
+    assert L.pir_combine_create(0, 4, 100, C.byref(h)) == _capi.PIR_ERR_BAD_ARG
+    assert L.pir_server_create(devs, 0, 1024, 32, 1, C.byref(h)) == _capi.PIR_ERR_BAD_ARG
