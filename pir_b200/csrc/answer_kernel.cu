@@ -483,7 +483,8 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
         gs++;                                                                       \
     }
         if (!warp_live) {
-            for (uint32_t q = 0; q < n_slices; q++) PUBLISH(0u)
+            if (NCB != 0)
+                for (uint32_t q = 0; q < n_slices; q++) PUBLISH(0u)
         } else {
             uint32_t tst = 0, d = 0, i = 0, bw = 0;
             while (true) {
@@ -510,7 +511,17 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
                     const uint32_t q = (i >> lp_log) - 1u;
                     uint32_t m = active ? 0xffffffffu : 0u;
                     if (!inside) m = active ? range_mask32(rowbase + ((uint64_t)q << slog), 1u << slog, first_row, end_row) : 0u;
-                    PUBLISH(bw & m)
+                    if (NCB != 0) {
+                        PUBLISH(bw & m)
+                    } else if (bw & m) {
+                        // BITS mode: the slice goes straight to the packed bit vector in global memory
+                        // (bit i = row first_row + i; the caller zeroed it).  A slice is at most 8 bits.
+                        const int64_t bit0 = (int64_t)(rowbase + ((uint64_t)q << slog)) - (int64_t)first_row;
+                        const int64_t w0 = bit0 >> 5;  // floor: rows below first_row carry no set bits
+                        const uint64_t sh = (uint64_t)(bw & m) << (uint32_t)(bit0 & 31);
+                        if ((uint32_t)sh) atomicOr(&ap.bits_out[w0], (uint32_t)sh);
+                        if ((uint32_t)(sh >> 32)) atomicOr(&ap.bits_out[w0 + 1], (uint32_t)(sh >> 32));
+                    }
                     bw = 0;
                 }
                 if (i == nlp) break;
@@ -525,7 +536,7 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
         it++;
     }
     // nothing left to expand: help the scan warps drain the ring
-    consume_slices<NCB>(ap, warp);
+    if constexpr (NCB != 0) consume_slices<NCB>(ap, warp);
     PHASE(c_tail)
 #undef PHASE
     if (ap.dbg && tid == 0) {
@@ -550,7 +561,8 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
     fill_tables(t0);
     uint32_t* red = red_words();
     const uint32_t words_out = (uint32_t)(ap.row_bytes >> 2);
-    for (uint32_t i = threadIdx.x; i < words_out; i += kAnswerThreads) red[i] = 0;
+    if constexpr (NCB != 0)
+        for (uint32_t i = threadIdx.x; i < words_out; i += kAnswerThreads) red[i] = 0;
     if (threadIdx.x == kAnswerThreads - 1) build_task_list(ap, reinterpret_cast<uint32_t*>(g_smem2 + kOffTasks));
     if (threadIdx.x == kAnswerThreads - 2) {
         for (uint32_t k = 0; k < kRing; k++) {
@@ -561,14 +573,17 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
         for (uint32_t k = 0; k < 1 + kRing; k++) claim[k] = 0;
     }
     __syncthreads();
-    if (threadIdx.x < kTreeThreads)
+    if (threadIdx.x < kTreeThreads) {
         tree_role<NCB>(qc, ap, lane_const(), c_entry);
-    else
-        consume_slices<NCB>(ap, threadIdx.x >> 5);
-    __syncthreads();
-    for (uint32_t i = threadIdx.x; i < words_out; i += kAnswerThreads) {
-        const uint32_t v = red[i];
-        if (v) atomicXor(&ap.out[i], v);
+    } else {
+        if constexpr (NCB != 0) consume_slices<NCB>(ap, threadIdx.x >> 5);
+    }
+    if constexpr (NCB != 0) {  // (BITS mode has nothing to fold)
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < words_out; i += kAnswerThreads) {
+            const uint32_t v = red[i];
+            if (v) atomicXor(&ap.out[i], v);
+        }
     }
 }
 
@@ -582,6 +597,7 @@ cudaError_t configure_answer_kernel() {
     if (e == cudaSuccess) e = cudaFuncSetAttribute(answer_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemEnd);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(answer_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemEnd);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(answer_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemEnd);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(answer_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemEnd);
     return e;
 }
 
@@ -600,7 +616,9 @@ cudaError_t launch_answer(const QueryConst& qc, const AnswerPlan& ap, const uint
     const uint64_t gmin = (chunks + (kMaxTasks - 1)) / kMaxTasks;
     if (g < gmin) g = gmin;
     const size_t smem = kSmemEnd - smem_base;
-    if (ap.row_bytes <= 512)
+    if (ap.bits_out)
+        answer_kernel<0><<<(unsigned)g, kAnswerThreads, smem, st>>>(qc, ap, d_t0);
+    else if (ap.row_bytes <= 512)
         answer_kernel<1><<<(unsigned)g, kAnswerThreads, smem, st>>>(qc, ap, d_t0);
     else if (ap.row_bytes == 1024)
         answer_kernel<2><<<(unsigned)g, kAnswerThreads, smem, st>>>(qc, ap, d_t0);

@@ -208,6 +208,8 @@ struct pir_db {
     uint64_t front_cap = 0;
     uint8_t* d_bits = nullptr;
     uint64_t bits_cap = 0;
+    uint32_t* d_bitmat = nullptr;  // batched path: [queries][words] packed selection bits
+    uint64_t bitmat_cap = 0;       // in words
     uint8_t* d_out = nullptr;
     uint64_t out_cap = 0;
     uint8_t* h_out = nullptr;  // pinned
@@ -422,6 +424,7 @@ extern "C" int pir_db_destroy(pir_db* db) {
         if (db->d_front_t[k]) cudaFree(db->d_front_t[k]);
     }
     if (db->d_bits) cudaFree(db->d_bits);
+    if (db->d_bitmat) cudaFree(db->d_bitmat);
     if (db->d_out) cudaFree(db->d_out);
     if (db->h_out) cudaFreeHost(db->h_out);
     if (db->d_keywords) cudaFree(db->d_keywords);
@@ -536,6 +539,8 @@ struct QueryGeom {
     uint64_t row_bytes;  // pitched
 };
 
+void fill_answer_split(pir_db* db, const QueryGeom& g, AnswerPlan* ap);
+
 int query_geom(const pir_db* db, const pir_query* q, QueryGeom* g) {
     if (!q) return fail(PIR_ERR_BAD_ARG, "query is null");
     if (q->reserved != 0) return fail(PIR_ERR_BAD_ARG, "pir_query.reserved must be 0");
@@ -574,23 +579,10 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
     static const bool use_v1 = getenv("PIRB_KERNEL") && !strcmp(getenv("PIRB_KERNEL"), "v1");
     if (!use_v1 && answer_kernel_supports(g.row_bytes, 0)) {
         // warp-specialised kernel: walks the top of the tree itself, one launch per query
-        if (db->split_nb != g.nb || db->split_first != g.first_row || db->split_rows != g.n_rows) {
-            const AnswerSplit sp = choose_answer_split(g.nb, g.first_row, g.n_rows, ctx.num_sms);
-            db->split_nb = g.nb;
-            db->split_first = g.first_row;
-            db->split_rows = g.n_rows;
-            db->split_dmax = sp.Dmax;
-            db->split_dmin = sp.Dmin;
-            db->split_b = sp.B;
-        }
         AnswerPlan ap{};
         ap.db = db->d_slots;
         ap.row_bytes = g.row_bytes;
-        ap.first_row = g.first_row;
-        ap.n_rows = g.n_rows;
-        ap.D = db->split_dmax;
-        ap.B = db->split_b;
-        ap.Dmin = db->split_dmin;
+        fill_answer_split(db, g, &ap);
         ap.out = (uint32_t*)d_out;
         if (const char* dbg = getenv("PIRB_DEBUG_FLAGS")) ap.pad = (uint32_t)atoi(dbg);  // timing experiments only
         static const bool phase_debug = getenv("PIRB_PHASE_DEBUG") != nullptr;
@@ -688,6 +680,88 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
     return PIR_OK;
 }
 
+// Fill the work-split fields of an AnswerPlan (cached per handle for the last (num_bits, rows) seen).
+void fill_answer_split(pir_db* db, const QueryGeom& g, AnswerPlan* ap) {
+    if (db->split_nb != g.nb || db->split_first != g.first_row || db->split_rows != g.n_rows) {
+        const AnswerSplit sp = choose_answer_split(g.nb, g.first_row, g.n_rows, db->ctx->num_sms);
+        db->split_nb = g.nb;
+        db->split_first = g.first_row;
+        db->split_rows = g.n_rows;
+        db->split_dmax = sp.Dmax;
+        db->split_dmin = sp.Dmin;
+        db->split_b = sp.B;
+    }
+    ap->first_row = g.first_row;
+    ap->n_rows = g.n_rows;
+    ap->D = db->split_dmax;
+    ap->B = db->split_b;
+    ap->Dmin = db->split_dmin;
+}
+
+// Should a batch of n index queries go through the two-phase path (bit vectors, then ONE pass over the
+// rows for all queries)?  It pays when the fused kernel would be bound by streaming the rows once per
+// query, i.e. for wide rows; PIRB_BATCH_MODE=fused|bits overrides.
+bool batch_uses_bits_path(const pir_db* db, const pir_query* qs, uint32_t n, const QueryGeom& g) {
+    if (qs[0].is_keyword || g.n_rows == 0) return false;
+    uint32_t tpq, segc, sr, qpl;
+    if (!batch_scan_geometry(g.row_bytes, &tpq, &segc, &sr, &qpl)) return false;
+    if (const char* e = getenv("PIRB_BATCH_MODE")) {
+        if (!strcmp(e, "fused")) return false;
+        if (!strcmp(e, "bits")) return true;
+    }
+    (void)db;
+    return n >= 4 && g.row_bytes >= 512;
+}
+
+// Two-phase batch: phase 1 expands every query into a packed bit vector (answer_kernel, BITS mode: no row
+// is read), phase 2 streams the shard once and folds every row into the accumulators of the queries that
+// selected it (batch_scan.cu).  d_out: n pitched answers, XOR-accumulated (zeroed here if zero_first).
+int enqueue_batch_bits(pir_db* db, const pir_query* qs, uint32_t n, const QueryGeom& g, uint8_t* d_out, cudaStream_t st,
+                       bool zero_first = true) {
+    const DeviceCtx& ctx = *db->ctx;
+    const uint64_t wpq = (((g.n_rows + 31) >> 5) + 1 + 3) & ~3ull;  // +1: a slice may spill into the next word
+    if ((uint64_t)n * wpq > db->bitmat_cap) {
+        if (db->d_bitmat) cudaFree(db->d_bitmat);
+        db->d_bitmat = nullptr;
+        db->bitmat_cap = 0;
+        CU(cudaMalloc(&db->d_bitmat, (uint64_t)n * wpq * 4));
+        db->bitmat_cap = (uint64_t)n * wpq;
+    }
+    CU(cudaMemsetAsync(db->d_bitmat, 0, (uint64_t)n * wpq * 4, st));
+    if (zero_first) CU(cudaMemsetAsync(d_out, 0, (uint64_t)n * g.row_bytes, st));
+    for (uint32_t i = 0; i < n; i++) {
+        QueryConst qc;
+        int rc = build_query_const(&qs[i], g.nb, &qc);
+        if (rc) return rc;
+        AnswerPlan ap{};
+        ap.db = db->d_slots;
+        ap.row_bytes = 16;  // unused in BITS mode
+        fill_answer_split(db, g, &ap);
+        ap.bits_out = db->d_bitmat + (uint64_t)i * wpq;
+        CU(launch_answer(qc, ap, ctx.d_t0, ctx.smem_base, ctx.num_sms, st));
+    }
+    uint32_t tpq, segc, sr, qpl;
+    batch_scan_geometry(g.row_bytes, &tpq, &segc, &sr, &qpl);
+    if (getenv("PIRB_BATCH_SKIP_SCAN")) return PIR_OK;  // timing experiments only (tools/batch_phases.py)
+    for (uint32_t q0 = 0; q0 < n; q0 += qpl) {
+        BatchScanPlan bp{};
+        bp.db = db->d_slots;
+        bp.row_bytes = g.row_bytes;
+        bp.n_rows = g.n_rows;
+        bp.bits = db->d_bitmat + (uint64_t)q0 * wpq;
+        bp.wpq = wpq;
+        bp.n_queries = n - q0 < qpl ? n - q0 : qpl;
+        bp.tpq = tpq;
+        bp.seg_chunks = segc;
+        bp.stage_rows = sr;
+        bp.rsplit = 1;
+        while (bp.rsplit < 32 && (uint64_t)bp.n_queries * tpq * (bp.rsplit * 2) <= 512) bp.rsplit *= 2;
+        bp.out = (uint32_t*)(d_out + (uint64_t)q0 * g.row_bytes);
+        CU(launch_batch_scan(bp, ctx.num_sms, st));
+    }
+    return PIR_OK;
+}
+
 // pitched device answer -> dense host answer (Shares[c].Data = out[c*S, (c+1)*S))
 void compact_answer(const pir_db* db, uint32_t W, const uint8_t* pitched, uint8_t* dense) {
     for (uint32_t c = 0; c < W; c++) memcpy(dense + (size_t)c * db->slot_bytes, pitched + (size_t)c * db->pitch, db->slot_bytes);
@@ -700,13 +774,18 @@ extern "C" int pir_answer_batch_device(pir_db* db, const pir_query* qs, uint32_t
     std::lock_guard<std::mutex> lk(db->mu);
     DeviceGuard g(db->device);
     cudaStream_t st = stream ? (cudaStream_t)stream : db->stream;
+    QueryGeom g0;
+    int rc = query_geom(db, &qs[0], &g0);
+    if (rc) return rc;
     for (uint32_t i = 0; i < n_queries; i++) {
         QueryGeom geom;
-        int rc = query_geom(db, &qs[i], &geom);
-        if (rc) return rc;
+        if ((rc = query_geom(db, &qs[i], &geom))) return rc;
         if (qs[i].group_size != qs[0].group_size || qs[i].is_keyword != qs[0].is_keyword)
             return fail(PIR_ERR_BAD_ARG, "all queries of a batch must share group_size and is_keyword");
-        rc = enqueue_answer(db, &qs[i], geom, (uint8_t*)d_out + (uint64_t)i * geom.row_bytes, st);
+    }
+    if (batch_uses_bits_path(db, qs, n_queries, g0)) return enqueue_batch_bits(db, qs, n_queries, g0, (uint8_t*)d_out, st);
+    for (uint32_t i = 0; i < n_queries; i++) {
+        rc = enqueue_answer(db, &qs[i], g0, (uint8_t*)d_out + (uint64_t)i * g0.row_bytes, st);
         if (rc) return rc;
     }
     return PIR_OK;
@@ -727,9 +806,18 @@ extern "C" int pir_answer_batch(pir_db* db, const pir_query* qs, uint32_t n_quer
         if ((rc = query_geom(db, &qs[i], &geom))) return rc;
         if (qs[i].group_size != qs[0].group_size || qs[i].is_keyword != qs[0].is_keyword)
             return fail(PIR_ERR_BAD_ARG, "all queries of a batch must share group_size and is_keyword");
-        if ((rc = enqueue_answer(db, &qs[i], geom, db->d_out + (uint64_t)i * geom.row_bytes, db->stream))) {
+    }
+    if (batch_uses_bits_path(db, qs, n_queries, g0)) {
+        if ((rc = enqueue_batch_bits(db, qs, n_queries, g0, db->d_out, db->stream))) {
             cudaStreamSynchronize(db->stream);
             return rc;
+        }
+    } else {
+        for (uint32_t i = 0; i < n_queries; i++) {
+            if ((rc = enqueue_answer(db, &qs[i], g0, db->d_out + (uint64_t)i * g0.row_bytes, db->stream))) {
+                cudaStreamSynchronize(db->stream);
+                return rc;
+            }
         }
     }
     CU(cudaMemcpyAsync(db->h_out, db->d_out, g0.row_bytes * n_queries, cudaMemcpyDeviceToHost, db->stream));

@@ -427,7 +427,9 @@ cudaError_t configure_kernels() {
     if ((e = set_max_smem(fused_kernel<N, true>)) != cudaSuccess) return e;
     PIRB_CFG(1) PIRB_CFG(2) PIRB_CFG(4) PIRB_CFG(8)
 #undef PIRB_CFG
-    return configure_answer_kernel();
+    e = configure_answer_kernel();
+    if (e == cudaSuccess) e = configure_batch_scan();
+    return e;
 }
 
 cudaError_t launch_top(const QueryConst& qc, const TopPlan& tp, const uint32_t* d_t0, uint32_t smem_base,

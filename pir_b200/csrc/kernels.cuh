@@ -42,7 +42,24 @@ struct AnswerPlan {
     uint32_t Dmin;        // chunk granularity of the CTA work split: chunks of 2^(B+Dmin+1) rows
     uint32_t pad;         // debug flags
     uint32_t* out;        // row_bytes/4 words, XOR-accumulated (atomics); the caller zeroes
+    uint32_t* bits_out;   // BITS mode (non-null): packed selection bits, bit i = row first_row + i, OR-accumulated
+                          // into a zeroed buffer of ceil(n_rows/32)+1 words; no rows are read
     unsigned long long* dbg;  // optional per-CTA phase cycle counters (PIRB_PHASE_DEBUG), else null
+};
+
+// Batched scan (batch_scan.cu): rows [0, n_rows) of a shard against n_queries packed bit vectors.
+struct BatchScanPlan {
+    const uint8_t* db;      // shard base
+    uint64_t row_bytes;     // multiple of 16, <= 32 KB
+    uint64_t n_rows;
+    const uint32_t* bits;   // [n_queries][wpq] packed selection bits (bit i of a vector = shard row i)
+    uint64_t wpq;           // words per query vector (>= ceil(n_rows / 32))
+    uint32_t n_queries;     // <= queries_per_launch of batch_scan_geometry
+    uint32_t tpq;           // threads per query (power of two)
+    uint32_t seg_chunks;    // 16-byte chunks per thread (<= 8)
+    uint32_t stage_rows;    // rows per shared-memory stage (power of two <= 32)
+    uint32_t rsplit;        // row classes (power of two <= 32): n_queries * tpq * rsplit <= 512
+    uint32_t* out;          // [n_queries][row_bytes / 4] words, XOR-accumulated; the caller zeroes
 };
 
 struct TopPlan {
@@ -88,6 +105,11 @@ cudaError_t launch_answer(const QueryConst& qc, const AnswerPlan& ap, const uint
 cudaError_t launch_signal_arrival(uint32_t* arrivals, cudaStream_t st);
 cudaError_t launch_wait_arrivals(const uint32_t* arrivals, uint32_t expected, uint64_t timeout_cycles,
                                  uint32_t* timed_out, cudaStream_t st);
+
+bool batch_scan_geometry(uint64_t row_bytes, uint32_t* tpq, uint32_t* seg_chunks, uint32_t* stage_rows,
+                         uint32_t* queries_per_launch);
+cudaError_t configure_batch_scan();
+cudaError_t launch_batch_scan(const BatchScanPlan& bp, int num_sms, cudaStream_t st);
 
 uint64_t launch_count();
 void count_launch();

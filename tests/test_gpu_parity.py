@@ -202,3 +202,34 @@ def test_error_paths(gpu_lib, capi):
         assert e.value.code == capi.PIR_ERR_UNSUPPORTED
     with pytest.raises(capi.PirError):
         Handle(0, 16)
+
+
+@pytest.mark.parametrize("db_size,slot_bytes,W,nq,first,count", [
+    (1 << 13, 1024, 1, 9, 0, None),        # the shape the heuristic sends down the two-phase path
+    (5000, 512, 1, 5, 0, None),            # non-power-of-two height
+    (3000, 100, 3, 4, 0, None),            # row of 336 bytes (not a power of two), group size 3
+    (1 << 12, 2048, 2, 17, 0, None),       # 4 KB rows: 16 queries per scan launch -> two scan launches
+    (40000, 256, 1, 70, 0, None),          # more queries than one scan launch of 64 x ... holds? (256 B: 256/launch)
+    (1 << 14, 1024, 1, 6, 5000, 7000),     # a shard whose first row is not a multiple of 32
+    (777, 16, 1, 8, 0, None),              # tiny rows
+])
+def test_batch_two_phase_path_matches_oracle(gpu_lib, monkeypatch, db_size, slot_bytes, W, nq, first, count):
+    """pir_answer_batch through the bit-vector + single-pass scan path (answer_kernel BITS mode +
+    batch_scan_kernel) equals the oracle answer of every query, and equals the fused path."""
+    data = oracle.synth_fill(21, 0, db_size, slot_bytes)
+    rows = db_size // W
+    rng = np.random.default_rng(nq)
+    idxs = [int(x) for x in rng.integers(0, rows, size=nq)]
+    pairs = [make_queries(100 + i, db_size, W, idx) for i, idx in enumerate(idxs)]
+    qs = [p[1][i & 1] for i, p in enumerate(pairs)]
+    os_ = [p[0][i & 1] for i, p in enumerate(pairs)]
+    with Handle(db_size, slot_bytes, slot_begin=first * W, slot_count=None if count is None else count * W) as h:
+        h.fill(21)
+        monkeypatch.setenv("PIRB_BATCH_MODE", "bits")
+        got = h.answer_batch(qs)
+        monkeypatch.setenv("PIRB_BATCH_MODE", "fused")
+        fused = h.answer_batch(qs)
+    assert np.array_equal(got, fused)
+    if count is None:
+        for i, o in enumerate(os_):
+            assert np.array_equal(got[i], oracle.answer(o, data, db_size, slot_bytes)), i
