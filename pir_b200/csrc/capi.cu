@@ -851,6 +851,24 @@ extern "C" int pir_expand_bits(pir_db* db, const pir_query* q, uint8_t* bits_out
             return fail(PIR_ERR_BAD_ARG, "keyword queries with group_size > 1 need an unsharded handle");
         CU(launch_eval_points(qc, db->d_keywords + (geom.first_row - db->slot_begin), 0, n_rows, nullptr,
                               db->d_bits, ctx.d_t0, ctx.smem_base, db->stream));
+    } else if (!getenv("PIRB_EXPAND_V1")) {
+        // answer kernel in BITS mode (packed bit vector, no rows read), then one byte per row
+        const uint64_t wpq = (((n_rows + 31) >> 5) + 1 + 3) & ~3ull;
+        if (wpq > db->bitmat_cap) {
+            if (db->d_bitmat) cudaFree(db->d_bitmat);
+            db->d_bitmat = nullptr;
+            db->bitmat_cap = 0;
+            CU(cudaMalloc(&db->d_bitmat, wpq * 4));
+            db->bitmat_cap = wpq;
+        }
+        CU(cudaMemsetAsync(db->d_bitmat, 0, wpq * 4, db->stream));
+        AnswerPlan ap{};
+        ap.db = db->d_slots;
+        ap.row_bytes = 16;
+        fill_answer_split(db, geom, &ap);
+        ap.bits_out = db->d_bitmat;
+        CU(launch_answer(qc, ap, ctx.d_t0, ctx.smem_base, ctx.num_sms, db->stream));
+        CU(launch_unpack_bits(db->d_bitmat, db->d_bits, n_rows, db->stream));
     } else {
         Plan p = make_plan(geom.nb, geom.first_row, geom.n_rows, ctx.num_sms);
         if ((rc = ensure_front(db, p.task_count + 2))) return rc;

@@ -513,6 +513,30 @@ cudaError_t launch_synth_fill(uint8_t* db, uint64_t slot_begin, uint64_t n_slots
     return cudaGetLastError();
 }
 
+// ---- packed selection bits -> one byte per row (Go's []bool, db.go:110-174) ------------------------
+__global__ void unpack_bits_kernel(const uint32_t* __restrict__ packed, uint8_t* __restrict__ bytes, uint64_t n_rows) {
+    // one thread per 4 rows: a 32-bit store of four 0/1 bytes
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; g * 4 < n_rows; g += stride) {
+        const uint32_t w = packed[g >> 3] >> ((g & 7) * 4);
+        const uint32_t v = (w & 1u) | ((w & 2u) << 7) | ((w & 4u) << 14) | ((w & 8u) << 21);
+        if (g * 4 + 4 <= n_rows) {
+            *reinterpret_cast<uint32_t*>(bytes + g * 4) = v;
+        } else {
+            for (uint64_t k = 0; g * 4 + k < n_rows; k++) bytes[g * 4 + k] = (uint8_t)((v >> (8 * k)) & 1u);
+        }
+    }
+}
+
+cudaError_t launch_unpack_bits(const uint32_t* packed, uint8_t* bytes, uint64_t n_rows, cudaStream_t st) {
+    if (n_rows == 0) return cudaSuccess;
+    uint64_t blocks = ((n_rows + 3) / 4 + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    unpack_bits_kernel<<<(unsigned)blocks, 256, 0, st>>>(packed, bytes, n_rows);
+    g_launches++;
+    return cudaGetLastError();
+}
+
 // ---- multi-GPU combine signalling --------------------------------------------------
 // A shard's answer kernel XORs its partial straight into the combine slot (possibly a peer GPU's memory,
 // red.global.xor over NVLink).  signal_arrival runs after it on the same stream: the partial is complete,

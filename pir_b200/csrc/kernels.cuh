@@ -101,6 +101,8 @@ uint64_t answer_chunks(uint64_t first_row, uint64_t n_rows, uint32_t B, uint32_t
 cudaError_t launch_answer(const QueryConst& qc, const AnswerPlan& ap, const uint32_t* d_t0, uint32_t smem_base,
                           int num_sms, cudaStream_t st);
 
+// packed bits (bit i = row i) -> one 0/1 byte per row; `bytes` must be 4-byte aligned
+cudaError_t launch_unpack_bits(const uint32_t* packed, uint8_t* bytes, uint64_t n_rows, cudaStream_t st);
 // multi-GPU combine signalling: bump / wait for a slot's arrival counter (system scope)
 cudaError_t launch_signal_arrival(uint32_t* arrivals, cudaStream_t st);
 cudaError_t launch_wait_arrivals(const uint32_t* arrivals, uint32_t expected, uint64_t timeout_cycles,
