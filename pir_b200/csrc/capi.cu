@@ -571,8 +571,12 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
         if (g.first_row < db->slot_begin || g.first_row + g.n_rows > db->slot_begin + db->slot_count)
             return fail(PIR_ERR_BAD_ARG, "keyword queries with group_size > 1 need an unsharded handle");
         if ((rc = ensure_bits(db, g.n_rows))) return rc;
-        CU(launch_eval_points(qc, db->d_keywords + (g.first_row - db->slot_begin), 0, g.n_rows, nullptr,
-                              db->d_bits, ctx.d_t0, ctx.smem_base, st));
+        if (getenv("PIRB_KEYWORD_V1"))
+            CU(launch_eval_points(qc, db->d_keywords + (g.first_row - db->slot_begin), 0, g.n_rows, nullptr,
+                                  db->d_bits, ctx.d_t0, ctx.smem_base, st));
+        else
+            CU(launch_keyword_walk(qc, db->d_keywords + (g.first_row - db->slot_begin), 0, g.n_rows, nullptr,
+                                   db->d_bits, ctx.d_t0, ctx.smem_base, ctx.num_sms, st));
         CU(launch_scan_bytes(db->d_slots, g.row_bytes, g.n_rows, db->d_bits, (uint32_t*)d_out, ctx.num_sms, st));
         return PIR_OK;
     }
@@ -849,8 +853,12 @@ extern "C" int pir_expand_bits(pir_db* db, const pir_query* q, uint8_t* bits_out
         if (!db->d_keywords) return fail(PIR_ERR_BAD_ARG, "keyword query on a database without keywords");
         if (geom.first_row < db->slot_begin || geom.first_row + geom.n_rows > db->slot_begin + db->slot_count)
             return fail(PIR_ERR_BAD_ARG, "keyword queries with group_size > 1 need an unsharded handle");
-        CU(launch_eval_points(qc, db->d_keywords + (geom.first_row - db->slot_begin), 0, n_rows, nullptr,
-                              db->d_bits, ctx.d_t0, ctx.smem_base, db->stream));
+        if (getenv("PIRB_KEYWORD_V1"))
+            CU(launch_eval_points(qc, db->d_keywords + (geom.first_row - db->slot_begin), 0, n_rows, nullptr,
+                                  db->d_bits, ctx.d_t0, ctx.smem_base, db->stream));
+        else
+            CU(launch_keyword_walk(qc, db->d_keywords + (geom.first_row - db->slot_begin), 0, n_rows, nullptr,
+                                   db->d_bits, ctx.d_t0, ctx.smem_base, ctx.num_sms, db->stream));
     } else if (!getenv("PIRB_EXPAND_V1")) {
         // answer kernel in BITS mode (packed bit vector, no rows read), then one byte per row
         const uint64_t wpq = (((n_rows + 31) >> 5) + 1 + 3) & ~3ull;
@@ -942,7 +950,9 @@ extern "C" int pir_dpf_eval_points(int device, const pir_query* q, const uint64_
     CU(cudaMalloc(&d_x, n * 8));
     cudaError_t e = cudaMalloc(&d_v, n * 8);
     if (e == cudaSuccess) e = cudaMemcpy(d_x, xs, n * 8, cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) e = launch_eval_points(qc, d_x, 0, n, d_v, nullptr, ctx->d_t0, ctx->smem_base, 0);
+    if (e == cudaSuccess)
+        e = getenv("PIRB_KEYWORD_V1") ? launch_eval_points(qc, d_x, 0, n, d_v, nullptr, ctx->d_t0, ctx->smem_base, 0)
+                                      : launch_keyword_walk(qc, d_x, 0, n, d_v, nullptr, ctx->d_t0, ctx->smem_base, ctx->num_sms, 0);
     if (e == cudaSuccess) e = cudaMemcpy(out, d_v, n * 8, cudaMemcpyDeviceToHost);
     cudaFree(d_x);
     if (d_v) cudaFree(d_v);

@@ -429,6 +429,7 @@ cudaError_t configure_kernels() {
 #undef PIRB_CFG
     e = configure_answer_kernel();
     if (e == cudaSuccess) e = configure_batch_scan();
+    if (e == cudaSuccess) e = configure_keyword_kernel();
     return e;
 }
 

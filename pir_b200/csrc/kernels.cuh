@@ -86,6 +86,10 @@ cudaError_t launch_fused(const QueryConst& qc, const FusedPlan& fp, bool bits_mo
 cudaError_t launch_eval_points(const QueryConst& qc, const uint64_t* xs, uint64_t x_first, uint64_t n,
                                int64_t* values, uint8_t* bits, const uint32_t* d_t0, uint32_t smem_base,
                                cudaStream_t st);
+// the same with prefix sharing between consecutive points (keyword_kernel.cu): the keyword path
+cudaError_t configure_keyword_kernel();
+cudaError_t launch_keyword_walk(const QueryConst& qc, const uint64_t* xs, uint64_t x_first, uint64_t n, int64_t* values,
+                                uint8_t* bits, const uint32_t* d_t0, uint32_t smem_base, int num_sms, cudaStream_t st);
 // masked XOR of rows from a byte-per-row bit vector (any row_bytes multiple of 16)
 cudaError_t launch_scan_bytes(const uint8_t* db, uint64_t row_bytes, uint64_t n_rows, const uint8_t* bits,
                               uint32_t* out, int num_sms, cudaStream_t st);

@@ -233,3 +233,40 @@ def test_batch_two_phase_path_matches_oracle(gpu_lib, monkeypatch, db_size, slot
     if count is None:
         for i, o in enumerate(os_):
             assert np.array_equal(got[i], oracle.answer(o, data, db_size, slot_bytes)), i
+
+
+@pytest.mark.parametrize("kind", ["dense_sorted", "duplicates", "unsorted", "clustered", "wide64"])
+def test_keyword_prefix_sharing_kernel_matches_oracle(gpu_lib, monkeypatch, kind):
+    """The keyword path restarts each row's walk below the last node it shares with the previous row
+    (keyword_kernel.cu).  Bits must equal the oracle's per-row 32-level Evaluate2P (db.go:132-147) for any
+    keyword order, with repeated keywords, and equal the plain per-row kernel."""
+    rng = np.random.default_rng(len(kind))
+    db_size, slot_bytes = 70000, 16
+    if kind == "dense_sorted":
+        kws = np.sort(rng.choice(1 << 20, size=db_size, replace=False).astype(np.uint64))
+    elif kind == "duplicates":
+        kws = np.sort(rng.integers(0, 5000, size=db_size).astype(np.uint64))
+    elif kind == "unsorted":
+        kws = rng.choice(1 << 32, size=db_size, replace=False).astype(np.uint64)
+    elif kind == "clustered":
+        base = rng.choice(1 << 32, size=70, replace=False).astype(np.uint64)
+        kws = np.sort((base[:, None] + np.arange(1000, dtype=np.uint64)[None, :]).reshape(-1) & np.uint64(0xffffffff))
+    else:  # keywords with bits above 2^32: only the low 32 bits select the path (getBit, dpf/common.go:56-58)
+        kws = np.sort(rng.integers(0, 1 << 62, size=db_size).astype(np.uint64))
+    target = 4242
+    (o0, o1), (q0, q1) = make_queries(9, db_size, 1, target, is_keyword=True, keyword=int(kws[target]) & 0xffffffff)
+    with Handle(db_size, slot_bytes) as h:
+        h.fill(3)
+        h.set_keywords(kws)
+        monkeypatch.delenv("PIRB_KEYWORD_V1", raising=False)
+        b0, b1 = h.expand_bits(q0), h.expand_bits(q1)
+        a0, a1 = h.answer(q0), h.answer(q1)
+        monkeypatch.setenv("PIRB_KEYWORD_V1", "1")
+        assert np.array_equal(h.expand_bits(q0), b0)
+    assert np.array_equal(b0, oracle.expand_shared_query(o0, db_size, keywords=kws))
+    assert np.array_equal(b1, oracle.expand_shared_query(o1, db_size, keywords=kws))
+    # rows whose keyword equals the target's (low 32 bits) are exactly the rows where the two servers' bits differ
+    same = (kws & np.uint64(0xffffffff)) == (kws[target] & np.uint64(0xffffffff))
+    assert np.array_equal((b0 ^ b1).astype(bool), same)
+    data = oracle.synth_fill(3, 0, db_size, slot_bytes)
+    assert np.array_equal(a0 ^ a1, np.bitwise_xor.reduce(data[same], axis=0))
