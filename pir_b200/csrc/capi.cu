@@ -1455,12 +1455,20 @@ extern "C" int pir_server_answer_batch(pir_server* s, const pir_query* qs, uint3
         std::lock_guard<std::mutex> lkdb(db->mu);
         DeviceGuard g(db->device);
         CU(cudaStreamWaitEvent(db->stream, s->zeroed, 0));
+        QueryGeom g0;
+        if ((rc = query_geom(db, &qs[0], &g0))) return rc;
         for (uint32_t k = 0; k < n_queries; k++) {
             if (qs[k].group_size != W || qs[k].is_keyword != qs[0].is_keyword)
                 return fail(PIR_ERR_BAD_ARG, "all queries of a batch must share group_size and is_keyword");
             QueryGeom geom;
             if ((rc = query_geom(db, &qs[k], &geom))) return rc;
-            if ((rc = enqueue_answer(db, &qs[k], geom, s->d_acc + (uint64_t)k * row_bytes, db->stream, false))) return rc;
+        }
+        if (batch_uses_bits_path(db, qs, n_queries, g0)) {
+            // two-phase batch per shard; its scan kernel XORs into the shared accumulator like the fused one
+            if ((rc = enqueue_batch_bits(db, qs, n_queries, g0, s->d_acc, db->stream, /*zero_first=*/false))) return rc;
+        } else {
+            for (uint32_t k = 0; k < n_queries; k++)
+                if ((rc = enqueue_answer(db, &qs[k], g0, s->d_acc + (uint64_t)k * row_bytes, db->stream, false))) return rc;
         }
         CU(cudaEventRecord(s->done[i], db->stream));
     }

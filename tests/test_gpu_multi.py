@@ -144,3 +144,18 @@ def test_combine_over_cuda_ipc_two_gpus(gpu_lib):
             pytest.fail("rank hung")
         assert p.exitcode == 0
     assert q.get(timeout=5) is True
+
+
+def test_server_batch_two_phase_over_shards(gpu_lib, monkeypatch):
+    """pir_server_answer_batch with wide rows: every shard runs the bit-vector + single-pass scan path and
+    XORs into the shared accumulator."""
+    db_size, S, nq = 1 << 13, 1024, 6
+    data = oracle.synth_fill(8, 0, db_size, S)
+    pairs = [make_queries(50 + i, db_size, 1, (i * 1237) % db_size) for i in range(nq)]
+    qs = [p[1][0] for p in pairs]
+    monkeypatch.setenv("PIRB_BATCH_MODE", "bits")
+    with sharding.Server(_devices(gpu_lib, 3), db_size, S) as srv:
+        srv.fill_synthetic(8)
+        got = srv.answer_batch(qs)
+    for i, p in enumerate(pairs):
+        assert np.array_equal(got[i], oracle.answer(p[0][0], data, db_size, S)), i

@@ -270,3 +270,28 @@ def test_keyword_prefix_sharing_kernel_matches_oracle(gpu_lib, monkeypatch, kind
     assert np.array_equal((b0 ^ b1).astype(bool), same)
     data = oracle.synth_fill(3, 0, db_size, slot_bytes)
     assert np.array_equal(a0 ^ a1, np.bitwise_xor.reduce(data[same], axis=0))
+
+
+def test_full_size_properties_2p24_x_256(gpu_lib):
+    """BASELINE.json configs[2] at full size (4 GiB), through size-independent properties: the two servers'
+    answers XOR to the queried slot (query.go:278-297), the answer equals the XOR of the four quarter-shard
+    partial answers (row sharding), ExpandSharedQuery's bits differ between the servers in
+    exactly one row, and PrivateSecretSharedQueryWithExpandedBits over those bits reproduces the answer."""
+    n, S = 1 << 24, 256
+    idx = 11_111_111
+    (o0, o1), (q0, q1) = make_queries(77, n, 1, idx)
+    with Handle(n, S) as h:
+        h.fill(2024)
+        a0, a1 = h.answer(q0), h.answer(q1)
+        want = h.download(idx, 1)[0]
+        assert np.array_equal(a0 ^ a1, want)
+        b0, b1 = h.expand_bits(q0), h.expand_bits(q1)
+        d = np.flatnonzero(b0 ^ b1)
+        assert d.tolist() == [idx]
+        assert np.array_equal(h.answer_with_bits(1, b0), a0)
+    acc = np.zeros(S, dtype=np.uint8)
+    for k in range(4):
+        with Handle(n, S, slot_begin=k * (n // 4), slot_count=n // 4) as hs:
+            hs.fill(2024)
+            acc ^= hs.answer(q0)
+    assert np.array_equal(acc, a0)
