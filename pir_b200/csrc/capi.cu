@@ -210,6 +210,8 @@ struct pir_db {
     uint64_t bits_cap = 0;
     uint32_t* d_bitmat = nullptr;  // batched path: [queries][words] packed selection bits
     uint64_t bitmat_cap = 0;       // in words
+    cudaStream_t side[2] = {nullptr, nullptr};  // batched path: phase-1 kernels alternate between two streams
+    cudaEvent_t side_ev[3] = {nullptr, nullptr, nullptr};
     uint8_t* d_out = nullptr;
     uint64_t out_cap = 0;
     uint8_t* h_out = nullptr;  // pinned
@@ -217,6 +219,7 @@ struct pir_db {
     // cached work split of the answer kernel for the last (num_bits, shard rows) seen
     uint32_t split_nb = 0, split_dmax = 0, split_dmin = 0, split_b = 0;
     uint64_t split_first = 0, split_rows = 0;
+    bool split_tp = false;
     // optional per-launch timing of the dominant (fused) kernel, for bench.py's roofline
     bool timing = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pool;
@@ -335,7 +338,9 @@ Plan make_plan(uint32_t nb, uint64_t first_row, uint64_t n_rows, int num_sms, in
 struct AnswerSplit {
     uint32_t Dmax, Dmin, B;
 };
-AnswerSplit choose_answer_split(uint32_t nb, uint64_t first_row, uint64_t n_rows, int num_sms) {
+// throughput: many independent launches run back to back on two streams (batches), so a CTA that finishes
+// early is replaced by one of the next launch: total work matters more than the slowest CTA.
+AnswerSplit choose_answer_split(uint32_t nb, uint64_t first_row, uint64_t n_rows, int num_sms, bool throughput = false) {
     AnswerSplit sp{};
     sp.B = nb - 1 < (uint32_t)kFusedLogThreads ? nb - 1 : (uint32_t)kFusedLogThreads;
     sp.Dmax = nb - 1 - sp.B < 7u ? nb - 1 - sp.B : 7u;
@@ -354,7 +359,7 @@ AnswerSplit choose_answer_split(uint32_t nb, uint64_t first_row, uint64_t n_rows
         const uint64_t C = answer_chunks(first_row, n_rows, sp.B, dmin);
         const uint64_t G = C < (uint64_t)num_sms ? C : (uint64_t)num_sms;
         const uint64_t cf = first_row >> (sp.B + dmin + 1);
-        double worst = 0.0;
+        double worst = 0.0, sum = 0.0;
         for (uint64_t b = 0; b < G; b++) {
             uint64_t cur = cf + b * C / G, end = cf + (b + 1) * C / G;
             double cost = 0.0;
@@ -369,9 +374,11 @@ AnswerSplit choose_answer_split(uint32_t nb, uint64_t first_row, uint64_t n_rows
                 cur += span;
             }
             if (cost > worst) worst = cost;
+            sum += cost;
         }
-        if (best < 0.0 || worst < best * 0.995) {
-            best = worst;
+        const double obj = throughput ? 0.75 * sum / (double)num_sms + 0.25 * worst : worst;
+        if (best < 0.0 || obj < best * 0.995) {
+            best = obj;
             sp.Dmin = dmin;
         }
     }
@@ -425,6 +432,10 @@ extern "C" int pir_db_destroy(pir_db* db) {
     }
     if (db->d_bits) cudaFree(db->d_bits);
     if (db->d_bitmat) cudaFree(db->d_bitmat);
+    for (int k = 0; k < 2; k++)
+        if (db->side[k]) cudaStreamDestroy(db->side[k]);
+    for (int k = 0; k < 3; k++)
+        if (db->side_ev[k]) cudaEventDestroy(db->side_ev[k]);
     if (db->d_out) cudaFree(db->d_out);
     if (db->h_out) cudaFreeHost(db->h_out);
     if (db->d_keywords) cudaFree(db->d_keywords);
@@ -539,7 +550,7 @@ struct QueryGeom {
     uint64_t row_bytes;  // pitched
 };
 
-void fill_answer_split(pir_db* db, const QueryGeom& g, AnswerPlan* ap);
+void fill_answer_split(pir_db* db, const QueryGeom& g, AnswerPlan* ap, bool throughput = false);
 
 int query_geom(const pir_db* db, const pir_query* q, QueryGeom* g) {
     if (!q) return fail(PIR_ERR_BAD_ARG, "query is null");
@@ -685,9 +696,10 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
 }
 
 // Fill the work-split fields of an AnswerPlan (cached per handle for the last (num_bits, rows) seen).
-void fill_answer_split(pir_db* db, const QueryGeom& g, AnswerPlan* ap) {
-    if (db->split_nb != g.nb || db->split_first != g.first_row || db->split_rows != g.n_rows) {
-        const AnswerSplit sp = choose_answer_split(g.nb, g.first_row, g.n_rows, db->ctx->num_sms);
+void fill_answer_split(pir_db* db, const QueryGeom& g, AnswerPlan* ap, bool throughput) {
+    if (db->split_nb != g.nb || db->split_first != g.first_row || db->split_rows != g.n_rows || db->split_tp != throughput) {
+        const AnswerSplit sp = choose_answer_split(g.nb, g.first_row, g.n_rows, db->ctx->num_sms, throughput);
+        db->split_tp = throughput;
         db->split_nb = g.nb;
         db->split_first = g.first_row;
         db->split_rows = g.n_rows;
@@ -733,6 +745,18 @@ int enqueue_batch_bits(pir_db* db, const pir_query* qs, uint32_t n, const QueryG
     }
     CU(cudaMemsetAsync(db->d_bitmat, 0, (uint64_t)n * wpq * 4, st));
     if (zero_first) CU(cudaMemsetAsync(d_out, 0, (uint64_t)n * g.row_bytes, st));
+    // Phase-1 kernels are independent; alternating them between two streams lets the CTAs of the next
+    // kernel start on SMs that the previous one has already left (each CTA fills an SM, so they never
+    // share one), which hides the ramp-down of every launch.
+    const bool two_streams = n >= 2 && !getenv("PIRB_BATCH_ONE_STREAM");
+    if (two_streams) {
+        for (int k = 0; k < 2; k++)
+            if (!db->side[k]) CU(cudaStreamCreateWithFlags(&db->side[k], cudaStreamNonBlocking));
+        for (int k = 0; k < 3; k++)
+            if (!db->side_ev[k]) CU(cudaEventCreateWithFlags(&db->side_ev[k], cudaEventDisableTiming));
+        CU(cudaEventRecord(db->side_ev[2], st));
+        for (int k = 0; k < 2; k++) CU(cudaStreamWaitEvent(db->side[k], db->side_ev[2], 0));
+    }
     for (uint32_t i = 0; i < n; i++) {
         QueryConst qc;
         int rc = build_query_const(&qs[i], g.nb, &qc);
@@ -740,10 +764,15 @@ int enqueue_batch_bits(pir_db* db, const pir_query* qs, uint32_t n, const QueryG
         AnswerPlan ap{};
         ap.db = db->d_slots;
         ap.row_bytes = 16;  // unused in BITS mode
-        fill_answer_split(db, g, &ap);
+        fill_answer_split(db, g, &ap, /*throughput=*/two_streams && n >= 4);
         ap.bits_out = db->d_bitmat + (uint64_t)i * wpq;
-        CU(launch_answer(qc, ap, ctx.d_t0, ctx.smem_base, ctx.num_sms, st));
+        CU(launch_answer(qc, ap, ctx.d_t0, ctx.smem_base, ctx.num_sms, two_streams ? db->side[i & 1] : st));
     }
+    if (two_streams)
+        for (int k = 0; k < 2; k++) {
+            CU(cudaEventRecord(db->side_ev[k], db->side[k]));
+            CU(cudaStreamWaitEvent(st, db->side_ev[k], 0));
+        }
     uint32_t tpq, segc, sr, qpl;
     batch_scan_geometry(g.row_bytes, &tpq, &segc, &sr, &qpl);
     if (getenv("PIRB_BATCH_SKIP_SCAN")) return PIR_OK;  // timing experiments only (tools/batch_phases.py)
