@@ -366,7 +366,7 @@ __device__ __forceinline__ void consume_slices(const AnswerPlan& ap, uint32_t wa
 }
 
 // ---- tree role ------------------------------------------------------------------------------------
-template <int NCB>
+template <int NCB, bool FCW_ODD>
 __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan& ap, uint32_t lc, long long c_entry) {
     const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31u;
     const uint32_t B = ap.B;
@@ -491,21 +491,30 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
                 const uint32_t lvl = lvl0 + d;
                 const uint32_t cw[4] = {qc.cw[lvl][0], qc.cw[lvl][1], qc.cw[lvl][2], qc.cw[lvl][3]};
                 const uint32_t cwtl = (uint32_t)(qc.cw_tl >> lvl) & 1u, cwtr = (uint32_t)(qc.cw_tr >> lvl) & 1u;
-                uint32_t a[3][4];
-                aes3_main_rounds(qc, s, lc, a);
-                if (d < D) {
-                    Children ch;
-                    inner_tail(qc, a, s, t, cw, cwtl, cwtr, lc, ch);
+                uint32_t pair;  // selection bits of the two leaves below a leaf parent
+                if (FCW_ODD || d < D) {
+                    uint32_t a[3][4];
+                    aes3_main_rounds(qc, s, lc, a);
+                    if (d < D) {
+                        Children ch;
+                        inner_tail(qc, a, s, t, cw, cwtl, cwtr, lc, ch);
 #pragma unroll
-                    for (int w = 0; w < 4; w++) stk[(d * 4 + w) * kTreeThreads + tid] = ch.sr[w];
-                    tst = (tst & ~(1u << d)) | (ch.tr << d);
+                        for (int w = 0; w < 4; w++) stk[(d * 4 + w) * kTreeThreads + tid] = ch.sr[w];
+                        tst = (tst & ~(1u << d)) | (ch.tr << d);
 #pragma unroll
-                    for (int w = 0; w < 4; w++) s[w] = ch.sl[w];
-                    t = ch.tl;
-                    d++;
-                    continue;
+                        for (int w = 0; w < 4; w++) s[w] = ch.sl[w];
+                        t = ch.tl;
+                        d++;
+                        continue;
+                    }
+                    pair = leaf_parent_tail(qc, a, s, t, cw, cwtl, cwtr, lc);
+                } else {
+                    // FinalCW even: the leaves' control bits do not matter, PRG block 2 is skipped
+                    uint32_t a2[2][4];
+                    aes2_main_rounds(qc, s, lc, a2);
+                    pair = leaf_parent_tail_even(qc, a2, s, t, cw, lc);
                 }
-                bw |= leaf_parent_tail(qc, a, s, t, cw, cwtl, cwtr, lc) << (2u * (i & ((1u << lp_log) - 1u)));
+                bw |= pair << (2u * (i & ((1u << lp_log) - 1u)));
                 i++;
                 if ((i & ((1u << lp_log) - 1u)) == 0) {  // a slice of every thread's rows is final: publish it
                     const uint32_t q = (i >> lp_log) - 1u;
@@ -547,7 +556,7 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
     }
 }
 
-template <int NCB>
+template <int NCB, bool FCW_ODD>
 __global__ void __launch_bounds__(kAnswerThreads, 1)
 answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ AnswerPlan ap,
               const uint32_t* __restrict__ t0) {
@@ -574,7 +583,7 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
     }
     __syncthreads();
     if (threadIdx.x < kTreeThreads) {
-        tree_role<NCB>(qc, ap, lane_const(), c_entry);
+        tree_role<NCB, FCW_ODD>(qc, ap, lane_const(), c_entry);
     } else {
         if constexpr (NCB != 0) consume_slices<NCB>(ap, threadIdx.x >> 5);
     }
@@ -592,12 +601,19 @@ bool answer_kernel_supports(uint64_t row_bytes, uint32_t D) {
     return D <= (uint32_t)kV2MaxDepth;
 }
 
+template <int NCB>
+static cudaError_t configure_answer_ncb() {
+    cudaError_t e = cudaFuncSetAttribute(answer_kernel<NCB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemEnd);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(answer_kernel<NCB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemEnd);
+    return e;
+}
+
 cudaError_t configure_answer_kernel() {
-    cudaError_t e = cudaFuncSetAttribute(answer_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemEnd);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(answer_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemEnd);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(answer_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemEnd);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(answer_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemEnd);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(answer_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemEnd);
+    cudaError_t e = configure_answer_ncb<0>();
+    if (e == cudaSuccess) e = configure_answer_ncb<1>();
+    if (e == cudaSuccess) e = configure_answer_ncb<2>();
+    if (e == cudaSuccess) e = configure_answer_ncb<4>();
+    if (e == cudaSuccess) e = configure_answer_ncb<8>();
     return e;
 }
 
@@ -616,16 +632,27 @@ cudaError_t launch_answer(const QueryConst& qc, const AnswerPlan& ap, const uint
     const uint64_t gmin = (chunks + (kMaxTasks - 1)) / kMaxTasks;
     if (g < gmin) g = gmin;
     const size_t smem = kSmemEnd - smem_base;
+    // two code paths per row geometry: keys with an odd FinalCW need the leaves' control bits, keys with an
+    // even one do not (aes_unrolled.cuh, leaf_parent_tail_even)
+    const bool odd = qc.fcw_parity != 0 || (ap.pad & 2u);
+#define PIRB_LAUNCH(NCB)                                                                           \
+    do {                                                                                           \
+        if (odd)                                                                                   \
+            answer_kernel<NCB, true><<<(unsigned)g, kAnswerThreads, smem, st>>>(qc, ap, d_t0);     \
+        else                                                                                       \
+            answer_kernel<NCB, false><<<(unsigned)g, kAnswerThreads, smem, st>>>(qc, ap, d_t0);    \
+    } while (0)
     if (ap.bits_out)
-        answer_kernel<0><<<(unsigned)g, kAnswerThreads, smem, st>>>(qc, ap, d_t0);
+        PIRB_LAUNCH(0);
     else if (ap.row_bytes <= 512)
-        answer_kernel<1><<<(unsigned)g, kAnswerThreads, smem, st>>>(qc, ap, d_t0);
+        PIRB_LAUNCH(1);
     else if (ap.row_bytes == 1024)
-        answer_kernel<2><<<(unsigned)g, kAnswerThreads, smem, st>>>(qc, ap, d_t0);
+        PIRB_LAUNCH(2);
     else if (ap.row_bytes == 2048)
-        answer_kernel<4><<<(unsigned)g, kAnswerThreads, smem, st>>>(qc, ap, d_t0);
+        PIRB_LAUNCH(4);
     else
-        answer_kernel<8><<<(unsigned)g, kAnswerThreads, smem, st>>>(qc, ap, d_t0);
+        PIRB_LAUNCH(8);
+#undef PIRB_LAUNCH
     count_launch();
     return cudaGetLastError();
 }

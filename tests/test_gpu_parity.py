@@ -295,3 +295,27 @@ def test_full_size_properties_2p24_x_256(gpu_lib):
             hs.fill(2024)
             acc ^= hs.answer(q0)
     assert np.array_equal(acc, a0)
+
+
+def test_both_final_cw_parities_are_covered(gpu_lib):
+    """The answer kernel has two code paths: keys whose FinalCW is odd need the leaves' control bits, keys
+    with an even FinalCW skip PRG block 2 at the leaf parents.  Both must equal the oracle, for both servers."""
+    db_size, slot_bytes = 1 << 15, 64
+    data = oracle.synth_fill(6, 0, db_size, slot_bytes)
+    seen = {0: 0, 1: 0}
+    seed = 1000
+    with Handle(db_size, slot_bytes) as h:
+        h.fill(6)
+        while min(seen.values()) < 3:
+            seed += 1
+            idx = (seed * 7919) % db_size
+            (o0, o1), (q0, q1) = make_queries(seed, db_size, 1, idx)
+            par = q0.final_cw & 1
+            if seen[par] >= 3:
+                continue
+            seen[par] += 1
+            a0, a1 = h.answer(q0), h.answer(q1)
+            assert np.array_equal(a0, oracle.answer(o0, data, db_size, slot_bytes)), (seed, par)
+            assert np.array_equal(a1, oracle.answer(o1, data, db_size, slot_bytes)), (seed, par)
+            assert np.array_equal(a0 ^ a1, data[idx])
+            assert np.array_equal(h.expand_bits(q0), oracle.expand_shared_query(o0, db_size)), (seed, par)
