@@ -93,10 +93,11 @@ cudaError_t configure_keyword_kernel() {
 cudaError_t launch_keyword_walk(const QueryConst& qc, const uint64_t* xs, uint64_t x_first, uint64_t n, int64_t* values,
                                 uint8_t* bits, const uint32_t* d_t0, uint32_t smem_base, int num_sms, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
-    // runs long enough to amortise the first full walk, short enough to give every thread work
-    uint64_t run_len = 64;
+    // one run per thread: the points are split evenly over all resident threads, so every SM gets the same
+    // number of points and the first (full) walk of a run is amortised over as many points as possible
     const uint64_t threads = (uint64_t)num_sms * kKwThreads;
-    while (run_len > 1 && (n + run_len - 1) / run_len < threads) run_len >>= 1;
+    uint64_t run_len = (n + threads - 1) / threads;
+    if (run_len < 1) run_len = 1;
     const uint64_t n_runs = (n + run_len - 1) / run_len;
     uint64_t blocks = (n_runs + kKwThreads - 1) / kKwThreads;
     if (blocks > (uint64_t)num_sms) blocks = (uint64_t)num_sms;
