@@ -333,6 +333,8 @@ __device__ __forceinline__ void consume_slices(const AnswerPlan& ap, uint32_t wa
     uint4 acc[NCB];
 #pragma unroll
     for (int cb = 0; cb < NCB; cb++) acc[cb] = make_uint4(0, 0, 0, 0);
+    long long c_wait = 0;
+    const long long c_in = ap.dbg ? clock64() : 0;
     while (true) {
         uint32_t u = 0;
         if (lane == 0) u = atomicAdd(claim, 1u);
@@ -349,7 +351,9 @@ __device__ __forceinline__ void consume_slices(const AnswerPlan& ap, uint32_t wa
         }
         if (!have) break;
         const uint32_t slot = gsl & (kRing - 1u), par = (gsl / kRing) & 1u;
+        const long long cw0 = (ap.dbg && warp_in_cta == kTreeWarps) ? clock64() : 0;
         mbar_wait(full_bar(slot), par);
+        if (ap.dbg && warp_in_cta == kTreeWarps) c_wait += clock64() - cw0;
         const uint32_t slog = slice_log(D);
         scan_group<(NCB >= 4 ? 8 : 16), NCB>(ap, sl, ring_words(slot), g, (int64_t)row_start - (int64_t)ap.first_row, D + 1u,
                        (gsl - gs0) << slog, list, acc);
@@ -361,6 +365,9 @@ __device__ __forceinline__ void consume_slices(const AnswerPlan& ap, uint32_t wa
                 mbar_arrive(empty_bar(slot));
             }
         }
+    }
+    if (ap.dbg && warp_in_cta == kTreeWarps && lane == 0) {  // first scan warp: cycles scanning vs waiting for slices
+        ap.dbg[11264ull + blockIdx.x] = ((unsigned long long)(clock64() - c_in - c_wait) << 32) | (unsigned long long)(c_wait & 0xffffffffll);
     }
     fold_acc<NCB>(sl, acc);
 }
@@ -543,6 +550,15 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
 #undef PUBLISH
         PHASE(c_dfs)
         it++;
+    }
+    if (ap.dbg && lane == 0) {  // spread of the tree warps' finishing times within the CTA
+        const unsigned long long te = (unsigned long long)(clock64() - c_entry);
+        atomicMax(ap.dbg + 8192ull + 2ull * blockIdx.x, te);
+        atomicMax(ap.dbg + 8192ull + 2ull * blockIdx.x + 1ull, (1ull << 40) - te);
+        // scan backlog at that moment: units published minus units claimed
+        const uint32_t claimed = *reinterpret_cast<volatile uint32_t*>(g_smem2 + (kAbsClaim - smem_addr(g_smem2)));
+        const uint32_t total_u = gs * kGroups;
+        atomicMax(ap.dbg + 10240ull + blockIdx.x, (unsigned long long)(total_u > claimed ? total_u - claimed : 0u) + 1ull);
     }
     // nothing left to expand: help the scan warps drain the ring
     if constexpr (NCB != 0) consume_slices<NCB>(ap, warp);

@@ -603,8 +603,8 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
         static const bool phase_debug = getenv("PIRB_PHASE_DEBUG") != nullptr;
         unsigned long long* d_dbg = nullptr;
         if (phase_debug) {
-            CU(cudaMalloc(&d_dbg, 8 * 8 * 1024));
-            CU(cudaMemsetAsync(d_dbg, 0, 8 * 8 * 1024, st));
+            CU(cudaMalloc(&d_dbg, 8 * 12 * 1024));
+            CU(cudaMemsetAsync(d_dbg, 0, 8 * 12 * 1024, st));
             ap.dbg = d_dbg;
         }
         cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -622,9 +622,9 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
         CU(launch_answer(qc, ap, ctx.d_t0, ctx.smem_base, ctx.num_sms, st));
         if (e1) CU(cudaEventRecord(e1, st));
         if (d_dbg) {  // development aid: average per-CTA cycles per phase of the tree warps, to stderr
-            std::vector<unsigned long long> h(8 * 1024);
+            std::vector<unsigned long long> h(12 * 1024);
             CU(cudaStreamSynchronize(st));
-            CU(cudaMemcpy(h.data(), d_dbg, 8 * 8 * 1024, cudaMemcpyDeviceToHost));
+            CU(cudaMemcpy(h.data(), d_dbg, 8 * 12 * 1024, cudaMemcpyDeviceToHost));
             cudaFree(d_dbg);
             double sum[8] = {0}, mx = 0;
             int n = 0;
@@ -639,6 +639,21 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
                     if (h[8 * b + 5])
                         fprintf(stderr, "[cta %d] tasks %llu prologue %llu top %llu bfs %llu dfs %llu tail %llu total %llu\n", b, h[8 * b + 6],
                                 h[8 * b + 7], h[8 * b + 0], h[8 * b + 1], h[8 * b + 3], h[8 * b + 4], h[8 * b + 5] + h[8 * b + 7]);
+            double spread = 0;
+            for (int b = 0; b < 1024; b++)
+                if (h[8 * b + 5]) spread += (double)h[8192 + 2 * b] - (double)((1ull << 40) - h[8192 + 2 * b + 1]);
+            double busy = 0, waitc = 0;
+            for (int b = 0; b < 1024; b++)
+                if (h[8 * b + 5]) {
+                    busy += (double)(h[11264 + b] >> 32);
+                    waitc += (double)(h[11264 + b] & 0xffffffffull);
+                }
+            if (n) fprintf(stderr, "[phase] first scan warp: %.0f cycles scanning, %.0f waiting for slices\n", busy / n, waitc / n);
+            double backlog = 0;
+            for (int b = 0; b < 1024; b++)
+                if (h[8 * b + 5]) backlog += (double)h[10240 + b] - 1.0;
+            if (n) fprintf(stderr, "[phase] scan backlog when a tree warp finishes (max over its warps): %.1f units of 32 words\n", backlog / n);
+            if (n) fprintf(stderr, "[phase] first-to-last tree warp done within a CTA: %.0f cycles (mean)\n", spread / n);
             if (n)
                 fprintf(stderr, "[phase] ctas %d tasks %.2f | prologue %.0f top %.0f bfs %.0f dfs %.0f (of which ring-full wait %.0f) tail %.0f | tree total %.0f cycles, slowest CTA %.0f\n",
                         n, sum[6] / n, sum[7] / n, sum[0] / n, sum[1] / n, sum[3] / n, sum[2] / n, sum[4] / n, sum[5] / n, mx);
