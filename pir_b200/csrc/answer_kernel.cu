@@ -2,12 +2,12 @@
 // (db.go:68-174 + dpf/server.go:55-101 + slot.go:19-30), warp-specialised for sm_100a.
 //
 // One persistent CTA per SM, 16 "tree" warps + kScanWarps "scan" warps:
-//   tree warps   per CTA task (an aligned subtree of 2^(B+d+1) rows, d <= 7): walk from the previous
-//                task's common ancestor to the task root, expand B levels breadth-first to 2^B thread
-//                roots, then every thread walks its own 2^(d+1)-row subtree depth-first (sibling stack in
-//                shared memory) with the unrolled T-table AES of aes_unrolled.cuh.  Selection bits are
-//                published in SLICES of 8 rows per thread into a ring of word buffers in shared memory.
-//                Tree warps never touch global memory in the steady state.
+//   tree warps   per CTA task (512 thread roots over consecutive rows, TaskShape below): expand the node
+//                range above the roots breadth-first from the tree root, then every thread walks its own
+//                2^(d+1)-row subtree depth-first (sibling stack in shared memory, d <= 7) with the
+//                unrolled T-table AES of aes_unrolled.cuh.  Selection bits are published in SLICES of 8
+//                rows per thread into a ring of word buffers in shared memory.  Tree warps never touch
+//                global memory in the steady state.
 //   scan warps   turn a slice's words into a compact list of selected rows (popc prefix sum per 32
 //                words) and stream exactly those rows from HBM with coalesced 128-bit loads (32/c rows
 //                per warp load for rows of c 16-byte chunks), XOR-accumulating in registers; rows whose
@@ -18,9 +18,9 @@
 // arrive, empty: the scan warps arrive).  The answer is reduced per CTA and XORed into global memory
 // (possibly a peer GPU's) with one atomic per word.
 //
-// Why deep tasks: the top of a task (walk + breadth-first levels) is executed by few warps and is bound
-// by single-warp issue latency (~1.7k cycles per level, ~28k cycles per task, measured), during which the
-// lookup pipe idles.  A thread that owns 2^(d+1) rows amortises it over 2^(d+1)-1 depth-first nodes.
+// Why deep tasks: the top of a task is executed by few warps and is bound by single-warp issue latency
+// (~1.7k cycles per level, measured), during which the lookup pipe idles.  A thread that owns 2^(d+1)
+// rows amortises it over 2^(d+1)-1 depth-first nodes.
 #include "kernels.cuh"
 #include "aes_unrolled.cuh"
 
@@ -36,16 +36,17 @@ constexpr int kV2MaxDepth = 7;                 // a thread owns at most 2^8 rows
 constexpr uint32_t kSliceLog = 3;              // rows per thread per slice (8), fewer for tiny depths
 constexpr uint32_t kRing = 8;                  // slice buffers in flight between tree and scan warps
 constexpr uint32_t kListEntries = 256;         // rows selected out of 32 words of a slice, per warp
-constexpr uint32_t kMaxTasks = 512;            // per CTA (launch_answer sizes the grid accordingly)
 
 // scratch below the tables (offsets from the dynamic shared memory base)
 constexpr uint32_t kOffStack = 0;                                   // [D<=7][4][512] u32 = 56 KB (aliases BFS)
 constexpr uint32_t kOffBfsS = 0;                                    // [2][512] uint4    = 16 KB
 constexpr uint32_t kOffBfsT = 16384;                                // [2][512] u8       =  1 KB
-constexpr uint32_t kOffPathS = kV2MaxDepth * 4 * kTreeThreads * 4;  // [65] uint4
-constexpr uint32_t kOffPathT = kOffPathS + 65 * 16;                 // [65] u32
-constexpr uint32_t kOffTasks = kOffPathT + 65 * 4 + 12;             // [1 + kMaxTasks] u32
-constexpr uint32_t kScratchEnd = kOffTasks + 4 + 4 * kMaxTasks;
+constexpr uint32_t kMaxTasks = 512;            // per CTA (launch_answer sizes the grid accordingly)
+constexpr uint32_t kOffPathS = kV2MaxDepth * 4 * kTreeThreads * 4;  // [65] uint4: the single-node levels above a task
+constexpr uint32_t kOffPathT = kOffPathS + 65 * 16;                 // [65] u8 (+ pad)
+constexpr uint32_t kOffTasks = kOffPathT + 80;                      // task list: header (n, base, stride) + [kMaxTasks] u32
+constexpr uint32_t kTaskHeader = 6;                                 // u32 words before the entries
+constexpr uint32_t kScratchEnd = kOffTasks + 4 * (kTaskHeader + kMaxTasks);
 // above the tables (absolute shared-window addresses)
 constexpr uint32_t kAbsLists = kTableEnd;                                      // [20 warps][256] u16
 constexpr uint32_t kAbsRing = kAbsLists + (kAnswerThreads / 32) * kListEntries * 2;  // [kRing][512] u32
@@ -125,12 +126,12 @@ __device__ __forceinline__ ScanLane scan_lane(const AnswerPlan& ap) {
 }
 
 // XOR the selected rows of words [g*32, g*32+32) of one slice buffer into acc.  Word `i` of the buffer
-// holds thread i's selection bits for its rows [slice_off, slice_off + 2^slice_log) of the task
-// (thread i owns task rows [i << rows_log, (i+1) << rows_log)).  `list` is a private 512-byte scratch of
-// the calling warp.
+// holds thread i's selection bits for its rows [slice_off, slice_off + 2^slice_log) (lane l of the group
+// owns rows [group_row0 + (l << rows_log), + 2^rows_log), numbered from the shard's first row).  `list` is
+// a private 512-byte scratch of the calling warp.
 template <int UNROLL, int NCB>
 __device__ __forceinline__ void scan_group(const AnswerPlan& ap, const ScanLane& sl, const uint32_t* wbuf,
-                                           uint32_t g, int64_t task_row0, uint32_t rows_log, uint32_t slice_off,
+                                           uint32_t g, int64_t group_row0, uint32_t rows_log, uint32_t slice_off,
                                            uint16_t* list, uint4 (&acc)[NCB]) {
     const uint32_t lane = threadIdx.x & 31u;
     uint32_t w = wbuf[g * 32u + lane];
@@ -145,7 +146,7 @@ __device__ __forceinline__ void scan_group(const AnswerPlan& ap, const ScanLane&
     if (total == 0) return;
     // byte address of the group's first row, for this lane's 16-byte chunk (rows before the shard's
     // first row are never selected, so a negative offset is never dereferenced)
-    const uint8_t* gbase = sl.lane_db + (task_row0 + ((int64_t)(g * 32u) << rows_log)) * (int64_t)ap.row_bytes;
+    const uint8_t* gbase = sl.lane_db + group_row0 * (int64_t)ap.row_bytes;
     // The list is kept as rpl interleaved sub-lists (entry p goes to sub-list p % rpl, the lane group that
     // will fetch it), so a lane group reads its next 8 row numbers with ONE 128-bit shared load.
     uint32_t pos = pre - cnt;
@@ -212,62 +213,134 @@ __device__ __forceinline__ void fold_acc(const ScanLane& sl, uint4 (&accs)[NCB])
 
 constexpr uint32_t kGroups = kTreeThreads / 32;  // 32-word groups per slice
 
+__host__ __device__ __forceinline__ uint64_t answer_tasks_of(uint64_t first_row, uint64_t n_rows, uint32_t D, uint32_t hi_warps) {
+    const uint64_t R = (uint64_t)(16u + hi_warps) << (D + 5u);
+    const uint64_t T0 = first_row & ~((2ull << D) - 1ull);
+    return (first_row + n_rows - T0 + R - 1ull) / R;
+}
+
 // ---- work split ---------------------------------------------------------------------------------------
-// The shard is cut into CHUNKS of 2^(B+Dmin+1) rows (a task whose threads own 2^(Dmin+1) rows each) and
-// CTA b owns the contiguous chunk range [b*C/G, (b+1)*C/G).  The CTA covers its range with aligned
-// power-of-two TASKS of 2^(B+d+1) rows, Dmin <= d <= Dmax, as large as alignment allows (binary
-// decomposition): most rows are expanded in deep tasks while the range boundaries sit on a fine grid, so
-// every CTA gets the same number of rows to within a chunk whatever the shard size.  Thread
-// kAnswerThreads-1 builds the CTA's task list once, smallest tasks first (whatever runs last is the part
-// whose scan is overlapped least, so the deep, many-slice tasks go last); both roles read it.
-struct TaskIter {
-    const uint32_t* list;  // shared: entry = (chunk offset from the CTA's first chunk) << 3 | d
-    uint64_t chunk0;
-    uint32_t n, pos, chunk_log;
-    __device__ __forceinline__ TaskIter(const AnswerPlan& ap, const uint32_t* task_list) {
-        list = task_list + 1;
-        n = task_list[0];
-        pos = 0;
-        chunk_log = ap.B + ap.Dmin + 1u;
+// A TASK is 512 thread roots over consecutive rows, of shape (D, hi_warps): the threads of the first
+// hi_warps tree warps own 2^(D+1) rows each, those of the other 16 - hi_warps warps half as many (their roots
+// sit one tree level lower), R = 2^(D+5) * (16 + hi_warps) rows in all: 512 * 2^(D+1) times 1, 7/8, 3/4 or
+// 5/8.  hi_warps is a multiple of 4: warp w runs on SM sub-partition w % 4 and the table-lookup rate is
+// capped per sub-partition (a CTA with 13..16 equally loaded warps takes the same time, measured), so
+// every sub-partition gets the same mix.  Tasks need not be aligned subtrees: the top of a task is a
+// breadth-first expansion of the node RANGE above its thread roots (tree_role).  Two ways to cover a shard,
+// chosen by the host against a cost model (capi.cu choose_answer_split):
+//   uniform (ap.hi_warps != 0)  every task has the shape (ap.D, ap.hi_warps); task t covers rows
+//            [T0 + t*R, T0 + (t+1)*R), T0 = first_row rounded down to a thread root, and CTA b runs tasks
+//            b, b + gridDim.x, ...  With R close to shard_rows / num_sms this is ONE task (one task top)
+//            per CTA on every SM: the split of choice for shards of a multi-GPU server.
+//   binary (ap.hi_warps == 0)   the shard is cut into CHUNKS of 2^(10+Dmin) rows, CTA b owns the contiguous
+//            chunk range [b*C/G, (b+1)*C/G) and covers it with aligned power-of-two tasks (shape (d, 16),
+//            Dmin <= d <= ap.D, as large as alignment allows), smallest first.  All 16 warps of a task do
+//            the same work, which the latency-sensitive even-FinalCW path likes: the split of choice when
+//            the uniform one would leave warps idle half of the time (large single-GPU databases).
+// Thread kAnswerThreads-1 writes the CTA's task list to shared memory once; both roles walk it.
+struct TaskShape {
+    uint32_t D, hiw;       // depth of the hi threads' subtrees; number of hi warps (4, 8, 12 or 16)
+    uint32_t m_hi, m_nom;  // hi thread roots; nodes of the hi roots' tree level the task spans (hi roots + lo parents)
+    uint32_t slog, n_slices_log;
+    uint64_t R;
+    __device__ __forceinline__ void set(uint32_t d, uint32_t hi_warps) {
+        D = d;
+        hiw = hi_warps;
+        m_hi = 32u * hiw;
+        m_nom = m_hi + 16u * (kTreeWarps - hiw);
+        slog = slice_log(D);
+        n_slices_log = D + 1u - slog;
+        R = (uint64_t)(kTreeWarps + hiw) << (D + 5u);
+    }
+    // first row, log2(rows per thread) and log2(rows per thread per slice) of tree warp g's threads
+    __device__ __forceinline__ void group_geom(uint32_t g, uint64_t row0, uint64_t& grow0, uint32_t& rows_log, uint32_t& gslog) const {
+        if (g < hiw) {
+            grow0 = row0 + ((uint64_t)(g * 32u) << (D + 1u));
+            rows_log = D + 1u;
+            gslog = slog;
+        } else {
+            grow0 = row0 + ((uint64_t)m_hi << (D + 1u)) + ((uint64_t)((g - hiw) * 32u) << D);
+            rows_log = D;
+            gslog = slog - 1u;
+        }
+    }
+};
+
+// number of tree levels above nodes [a, a + m) of level L that hold a single node (the common prefix of a and a+m-1)
+__device__ __forceinline__ uint32_t single_node_levels(uint32_t L, uint64_t a, uint32_t m) {
+    return L - (64u - (uint32_t)__clzll((long long)(a ^ (a + m - 1u))));  // (clzll(0) = 64)
+}
+
+// geometry of the binary split
+struct ChunkRange {
+    uint32_t chunk_log;
+    uint64_t c0, c1;  // this CTA's chunks
+    __device__ __forceinline__ ChunkRange(const AnswerPlan& ap) {
+        chunk_log = 10u + ap.Dmin;
         const uint64_t end_row = ap.first_row + ap.n_rows;
         const uint64_t cf = ap.first_row >> chunk_log, cl = (end_row + ((1ull << chunk_log) - 1ull)) >> chunk_log;
-        chunk0 = cf + (uint64_t)blockIdx.x * (cl - cf) / gridDim.x;
+        c0 = cf + (uint64_t)blockIdx.x * (cl - cf) / gridDim.x;
+        c1 = cf + (uint64_t)(blockIdx.x + 1) * (cl - cf) / gridDim.x;
     }
-    __device__ __forceinline__ bool next(uint64_t& row_start, uint32_t& d) {
-        if (pos >= n) return false;
-        const uint32_t e = list[pos++];
-        d = e & 7u;
-        row_start = (chunk0 + (e >> 3)) << chunk_log;
-        return true;
+};
+
+// The CTA's task list in shared memory: n, then (64-bit) base and stride, then n entries
+// (offset << 5 | (hi_warps/4 - 1) << 3 | d); a task's first row is base + offset * stride.
+struct TaskIter {
+    const uint32_t* list;
+    uint32_t n, pos;
+    __device__ __forceinline__ TaskIter(const uint32_t* task_list) : list(task_list), n(task_list[0]), pos(0) {}
+    __device__ __forceinline__ void decode(uint32_t k, uint64_t& row_start, TaskShape& ts) const {
+        const uint32_t e = list[kTaskHeader + k];
+        const uint64_t base = *reinterpret_cast<const uint64_t*>(list + 2), stride = *reinterpret_cast<const uint64_t*>(list + 4);
+        ts.set(e & 7u, 4u * (((e >> 3) & 3u) + 1u));
+        row_start = base + (uint64_t)(e >> 5) * stride;
     }
-    __device__ __forceinline__ bool exhausted() const { return pos >= n; }
+    __device__ __forceinline__ uint32_t slices_log(uint32_t k) const {  // log2(slices of task k)
+        const uint32_t d = list[kTaskHeader + k] & 7u;
+        return d + 1u - slice_log(d);
+    }
 };
 
 __device__ __forceinline__ void build_task_list(const AnswerPlan& ap, uint32_t* task_list) {
-    const uint32_t chunk_log = ap.B + ap.Dmin + 1u;
-    const uint64_t end_row = ap.first_row + ap.n_rows;
-    const uint64_t cf = ap.first_row >> chunk_log, cl = (end_row + ((1ull << chunk_log) - 1ull)) >> chunk_log;
-    const uint64_t C = cl - cf;
-    const uint64_t c0 = cf + (uint64_t)blockIdx.x * C / gridDim.x, c1 = cf + (uint64_t)(blockIdx.x + 1) * C / gridDim.x;
     uint32_t n = 0;
-    for (uint32_t want = ap.Dmin; want <= ap.D; want++) {
-        uint64_t cur = c0;
-        while (cur < c1) {
-            uint32_t d = ap.Dmin;
-            uint64_t span = 1;
-            while (d < ap.D && !(cur & (2ull * span - 1ull)) && cur + 2ull * span <= c1) {
-                d++;
-                span *= 2ull;
+    uint64_t base, stride;
+    uint32_t* entries = task_list + kTaskHeader;
+    if (ap.hi_warps) {
+        TaskShape ts;
+        ts.set(ap.D, ap.hi_warps);
+        base = (ap.first_row & ~((2ull << ap.D) - 1ull)) + (uint64_t)blockIdx.x * ts.R;
+        stride = (uint64_t)gridDim.x * ts.R;
+        const uint64_t NT = answer_tasks_of(ap.first_row, ap.n_rows, ap.D, ap.hi_warps);
+        if (blockIdx.x < NT) n = (uint32_t)((NT - blockIdx.x + gridDim.x - 1ull) / gridDim.x);
+        if (n > kMaxTasks) __trap();  // launch_answer sizes the grid so that this cannot happen
+        for (uint32_t k = 0; k < n; k++) entries[k] = (k << 5) | ((ap.hi_warps / 4u - 1u) << 3) | ap.D;
+    } else {
+        const ChunkRange cr(ap);
+        base = cr.c0 << cr.chunk_log;
+        stride = 1ull << cr.chunk_log;
+        for (uint32_t want = ap.Dmin; want <= ap.D; want++) {  // smallest tasks first: whatever runs last is the
+            uint64_t cur = cr.c0;                             // part whose scan is overlapped least
+            while (cur < cr.c1) {
+                uint32_t d = ap.Dmin;
+                uint64_t span = 1;
+                while (d < ap.D && !(cur & (2ull * span - 1ull)) && cur + 2ull * span <= cr.c1) {
+                    d++;
+                    span *= 2ull;
+                }
+                if (d == want) {
+                    if (n >= kMaxTasks) __trap();
+                    entries[n++] = ((uint32_t)(cur - cr.c0) << 5) | (3u << 3) | d;
+                }
+                cur += span;
             }
-            if (d == want) {
-                if (n >= kMaxTasks) __trap();  // launch_answer sizes the grid so that this cannot happen
-                task_list[1 + n++] = ((uint32_t)(cur - c0) << 3) | d;
-            }
-            cur += span;
         }
     }
     task_list[0] = n;
+    *reinterpret_cast<uint64_t*>(task_list + 2) = base;
+    *reinterpret_cast<uint64_t*>(task_list + 4) = stride;
 }
+
 // ---- cooperative node expansion for the narrow top of a task --------------------------------------
 // One warp executing a whole 3-block PRG is bound by its own SMSP's ALU rate (~2500 cycles per level).
 // Near the root only a few nodes exist, so three warps on three SMSPs each take ONE AES block of the
@@ -311,7 +384,6 @@ __device__ __forceinline__ void coop_block(const QueryConst& qc, uint32_t k, uin
     }
 }
 
-constexpr uint32_t kCoopMaxLevel = 6;  // breadth-first levels with <= 64 nodes use coop_block
 
 // ---- consumer loop (scan warps all along, tree warps once they have nothing left to expand) ----------
 // Work unit = one 32-word group of one slice, claimed in order from a shared counter, so the backlog at
@@ -325,11 +397,9 @@ __device__ __forceinline__ void consume_slices(const AnswerPlan& ap, uint32_t wa
     uint16_t* list = reinterpret_cast<uint16_t*>(g_smem2 + (kAbsLists - dyn_base)) + warp_in_cta * kListEntries;
     uint32_t* claim = reinterpret_cast<uint32_t*>(g_smem2 + (kAbsClaim - dyn_base));
     uint32_t* done = claim + 1;
-    const uint32_t* task_list = reinterpret_cast<const uint32_t*>(g_smem2 + kOffTasks);
-    TaskIter ti(ap, task_list);
-    uint64_t row_start = 0;
-    uint32_t D = 0;
-    uint32_t gs0 = 0, gs1 = 0;  // global slice range of the current task
+    // (only pos, gs0, gs1 stay in registers across scan_group, whose 16 loads in flight need the rest)
+    TaskIter ti(reinterpret_cast<const uint32_t*>(g_smem2 + kOffTasks));
+    uint32_t gs0 = 0, gs1 = 0;  // global slice range of the current task (task ti.pos - 1)
     uint4 acc[NCB];
 #pragma unroll
     for (int cb = 0; cb < NCB; cb++) acc[cb] = make_uint4(0, 0, 0, 0);
@@ -342,21 +412,28 @@ __device__ __forceinline__ void consume_slices(const AnswerPlan& ap, uint32_t wa
         const uint32_t gsl = u / kGroups, g = u % kGroups;
         bool have = true;
         while (gsl >= gs1) {  // advance to the task that owns this slice
-            if (!ti.next(row_start, D)) {
+            if (ti.pos >= ti.n) {
                 have = false;
                 break;
             }
             gs0 = gs1;
-            gs1 += 1u << (D + 1u - slice_log(D));
+            gs1 += 1u << ti.slices_log(ti.pos++);
         }
         if (!have) break;
         const uint32_t slot = gsl & (kRing - 1u), par = (gsl / kRing) & 1u;
         const long long cw0 = (ap.dbg && warp_in_cta == kTreeWarps) ? clock64() : 0;
         mbar_wait(full_bar(slot), par);
         if (ap.dbg && warp_in_cta == kTreeWarps) c_wait += clock64() - cw0;
-        const uint32_t slog = slice_log(D);
-        scan_group<(NCB >= 4 ? 8 : 16), NCB>(ap, sl, ring_words(slot), g, (int64_t)row_start - (int64_t)ap.first_row, D + 1u,
-                       (gsl - gs0) << slog, list, acc);
+        uint64_t grow0;
+        uint32_t rows_log, gslog;
+        {
+            TaskShape ts;
+            uint64_t row_start;
+            ti.decode(ti.pos - 1u, row_start, ts);
+            ts.group_geom(g, row_start, grow0, rows_log, gslog);
+        }
+        scan_group<(NCB >= 4 ? 8 : 16), NCB>(ap, sl, ring_words(slot), g, (int64_t)grow0 - (int64_t)ap.first_row, rows_log,
+                       (gsl - gs0) << gslog, list, acc);
         __syncwarp();
         if (lane == 0) {
             __threadfence_block();
@@ -376,18 +453,20 @@ __device__ __forceinline__ void consume_slices(const AnswerPlan& ap, uint32_t wa
 template <int NCB, bool FCW_ODD>
 __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan& ap, uint32_t lc, long long c_entry) {
     const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31u;
-    const uint32_t B = ap.B;
     const uint32_t top_bits = qc.num_bits - 1u;  // rows are (num_bits-1)-bit numbers: the top level always goes left
     const uint64_t first_row = ap.first_row, end_row = ap.first_row + ap.n_rows;
     uint32_t* stk = reinterpret_cast<uint32_t*>(g_smem2 + kOffStack);
     uint4* bfs_s = reinterpret_cast<uint4*>(g_smem2 + kOffBfsS);
     uint8_t* bfs_t = g_smem2 + kOffBfsT;
+
     uint4* path_s = reinterpret_cast<uint4*>(g_smem2 + kOffPathS);
     uint8_t* path_t = g_smem2 + kOffPathT;
 
-    TaskIter ti(ap, reinterpret_cast<const uint32_t*>(g_smem2 + kOffTasks));
-    uint64_t row_start = 0, row_prev = 0;
-    uint32_t D = 0, Fc_prev = 0, it = 0;
+    // (nothing about the task sequence is kept in registers across the depth-first loop but `it`: the
+    //  geometry of the current and of the previous task is re-derived from the list in shared memory)
+    const TaskIter ti(reinterpret_cast<const uint32_t*>(g_smem2 + kOffTasks));
+    const uint32_t n_tasks = ti.n;
+    uint32_t it = 0;
     uint32_t gs = 0;  // slices published so far (ring position)
     long long c_top = 0, c_bfs = 0, c_dfs = 0, c_tail = 0, c_pub = 0, c_mark = clock64();
     const long long c_begin = c_mark;
@@ -397,16 +476,26 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
         acc += now_ - c_mark;                   \
         c_mark = now_;                          \
     }
-    while (ti.next(row_start, D)) {
-        const uint32_t Fc = top_bits - D - B;        // tree level of the task root
-        const uint32_t lvl0 = Fc + B;
+    for (; it < n_tasks; it++) {
+        TaskShape ts;
+        uint64_t row_start;
+        ti.decode(it, row_start, ts);
+        const uint32_t L = top_bits - ts.D;  // tree level of the hi thread roots (2^L nodes, 2^(D+1) rows each)
+        const bool hi = warp < ts.hiw;
+        const uint32_t D = hi ? ts.D : ts.D - 1u;     // depth of this thread's own subtree (warp-uniform)
+        const uint32_t lvl0 = hi ? L : L + 1u;        // tree level of this thread's root
         const uint32_t nlp = 1u << D;                // leaf parents per thread
-        const uint32_t rows_log = D + 1;
-        const uint32_t slog = slice_log(D), lp_log = slog - 1u;
-        const uint64_t p = row_start >> (B + rows_log);  // node index at level Fc
-        // -- top walk: re-expand from the common ancestor with the previous task's root (3 warps) --
+        const uint32_t rows_log = D + 1u;
+        const uint32_t slog = hi ? ts.slog : ts.slog - 1u, lp_log = slog - 1u;
+        // the task spans nodes [a, a + m) of level L: hi roots first, then the parents of the lo roots
+        const uint64_t a = row_start >> (ts.D + 1u);
+        const uint32_t m = (a + ts.m_nom <= (1ull << L)) ? ts.m_nom : (uint32_t)((1ull << L) - a);
         const uint32_t ck = warp & 3u, cj = (warp >> 2) * 32u + lane;  // coop role: block ck of node cj
         const bool coop_warp = ck < 3u && warp < 8u;
+        // -- the top, part 1: levels with a single node above the range (the common prefix of a and a+m-1).
+        //    They are kept in path_s/path_t, and the walk restarts below the last node shared with the
+        //    previous task. --
+        const uint32_t Ls = single_node_levels(L, a, m);
         {
             uint32_t cp = 0;
             if (it == 0) {
@@ -416,15 +505,22 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
                 }
                 bar_sync(BAR_TREE, kTreeThreads);
             } else {
-                // levels whose path entries are still valid: the common prefix of the two first rows,
-                // capped by how deep the previous and the current walk go
-                cp = top_bits - (64u - (uint32_t)__clzll((long long)(row_start ^ row_prev)));
-                cp = cp < Fc_prev ? cp : Fc_prev;
-                cp = cp < Fc ? cp : Fc;
+                // common leading bits of the two tasks' first rows (as top_bits+1-bit numbers), capped by how
+                // deep the previous and the current single-node walks go
+                TaskShape tp;
+                uint64_t row_prev;
+                ti.decode(it - 1u, row_prev, tp);
+                const uint32_t Lp = top_bits - tp.D;
+                const uint64_t ap_ = row_prev >> (tp.D + 1u);
+                const uint32_t mp = (ap_ + tp.m_nom <= (1ull << Lp)) ? tp.m_nom : (uint32_t)((1ull << Lp) - ap_);
+                const uint32_t Ls_prev = single_node_levels(Lp, ap_, mp);
+                cp = top_bits + 1u - (64u - (uint32_t)__clzll((long long)(row_start ^ row_prev)));
+                cp = cp < Ls_prev ? cp : Ls_prev;
+                cp = cp < Ls ? cp : Ls;
             }
-            for (uint32_t l = cp; l < Fc; l++) {
+            for (uint32_t l = cp; l < Ls; l++) {
                 if (coop_warp && cj == 0) {
-                    const uint32_t bit = (uint32_t)(p >> (Fc - 1 - l)) & 1u;
+                    const uint32_t bit = (uint32_t)(a >> (L - 1u - l)) & 1u;
                     uint8_t* ds = reinterpret_cast<uint8_t*>(&path_s[l + 1]);
                     coop_block(qc, ck, path_s[l], path_t[l], l, lc, bit ? nullptr : ds, bit ? nullptr : &path_t[l + 1],
                                bit ? ds : nullptr, bit ? &path_t[l + 1] : nullptr);
@@ -432,51 +528,91 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
                 bar_sync(BAR_TREE, kTreeThreads);
             }
             if (tid == 0) {
-                bfs_s[0] = path_s[Fc];
-                bfs_t[0] = path_t[Fc];
+                bfs_s[(Ls & 1u) * kTreeThreads] = path_s[Ls];
+                bfs_t[(Ls & 1u) * kTreeThreads] = path_t[Ls];
             }
         }
-        row_prev = row_start;
-        Fc_prev = Fc;
         bar_sync(BAR_TREE, kTreeThreads);
-        PHASE(c_top)
-        // -- B breadth-first levels: 2^B thread roots --
-        for (uint32_t b = 0; b < B; b++) {
-            const uint32_t o = ((b + 1) & 1) * kTreeThreads;
-            if (b <= kCoopMaxLevel) {
-                if (coop_warp && cj < (1u << b)) {
-                    uint8_t* cs = reinterpret_cast<uint8_t*>(&bfs_s[o + 2 * cj]);
-                    coop_block(qc, ck, bfs_s[(b & 1) * kTreeThreads + cj], bfs_t[(b & 1) * kTreeThreads + cj], Fc + b, lc,
-                               cs, &bfs_t[o + 2 * cj], cs + 16, &bfs_t[o + 2 * cj + 1]);
+        // -- part 2: breadth-first over the node range, level by level.  Level l holds nodes
+        //    [a >> (L-l), (a+m-1) >> (L-l)]; a child is kept if it falls into the next level's range. --
+        for (uint32_t l = Ls; l < L; l++) {
+            const uint32_t sh = L - l;
+            const uint64_t lo = a >> sh, lo2 = a >> (sh - 1u);
+            const uint32_t n = (uint32_t)(((a + m - 1u) >> sh) - lo) + 1u;
+            const uint32_t n2 = (uint32_t)(((a + m - 1u) >> (sh - 1u)) - lo2) + 1u;
+            const uint32_t skip = (uint32_t)(lo2 - 2ull * lo);  // 1: the first node's left child is out of range
+            const uint32_t src = (l & 1u) * kTreeThreads, dst = ((l + 1u) & 1u) * kTreeThreads;
+            if (n <= 64u) {
+                if (coop_warp && cj < n) {
+                    const uint32_t li = 2u * cj - skip, ri = li + 1u;  // (li wraps when the left child is skipped)
+                    const bool lv = (cj > 0u || skip == 0u) && li < n2, rv = ri < n2;
+                    uint8_t* ls = reinterpret_cast<uint8_t*>(&bfs_s[dst + li]);
+                    uint8_t* rs = reinterpret_cast<uint8_t*>(&bfs_s[dst + ri]);
+                    coop_block(qc, ck, bfs_s[src + cj], bfs_t[src + cj], l, lc, lv ? ls : nullptr, lv ? &bfs_t[dst + li] : nullptr,
+                               rv ? rs : nullptr, rv ? &bfs_t[dst + ri] : nullptr);
                 }
-            } else if (tid < (1u << b)) {
-                const uint4 sv = bfs_s[(b & 1) * kTreeThreads + tid];
-                const uint32_t s[4] = {sv.x, sv.y, sv.z, sv.w};
+            } else if (tid < n) {
+                const uint4 sv = bfs_s[src + tid];
+                const uint32_t sw[4] = {sv.x, sv.y, sv.z, sv.w};
                 Children ch;
-                expand_node<1>(qc, s, bfs_t[(b & 1) * kTreeThreads + tid], Fc + b, lc, ch);
-                bfs_s[o + 2 * tid] = make_uint4(ch.sl[0], ch.sl[1], ch.sl[2], ch.sl[3]);
-                bfs_s[o + 2 * tid + 1] = make_uint4(ch.sr[0], ch.sr[1], ch.sr[2], ch.sr[3]);
-                bfs_t[o + 2 * tid] = (uint8_t)ch.tl;
-                bfs_t[o + 2 * tid + 1] = (uint8_t)ch.tr;
+                expand_node<1>(qc, sw, bfs_t[src + tid], l, lc, ch);
+                const uint32_t li = 2u * tid - skip, ri = li + 1u;
+                if ((tid > 0u || skip == 0u) && li < n2) {
+                    bfs_s[dst + li] = make_uint4(ch.sl[0], ch.sl[1], ch.sl[2], ch.sl[3]);
+                    bfs_t[dst + li] = (uint8_t)ch.tl;
+                }
+                if (ri < n2) {
+                    bfs_s[dst + ri] = make_uint4(ch.sr[0], ch.sr[1], ch.sr[2], ch.sr[3]);
+                    bfs_t[dst + ri] = (uint8_t)ch.tr;
+                }
+            }
+            bar_sync(BAR_TREE, kTreeThreads);
+        }
+        PHASE(c_top)
+        // -- the lo roots: one more level below the nodes [m_hi, m) --
+        const uint32_t P = (L & 1u) * kTreeThreads, Q = ((L + 1u) & 1u) * kTreeThreads;
+        const uint32_t n_par = m > ts.m_hi ? m - ts.m_hi : 0u;
+        if (n_par) {
+            if (n_par <= 64u) {
+                if (coop_warp && cj < n_par) {
+                    uint8_t* cs = reinterpret_cast<uint8_t*>(&bfs_s[Q + 2u * cj]);
+                    coop_block(qc, ck, bfs_s[P + ts.m_hi + cj], bfs_t[P + ts.m_hi + cj], L, lc, cs, &bfs_t[Q + 2u * cj], cs + 16,
+                               &bfs_t[Q + 2u * cj + 1u]);
+                }
+            } else if (tid < n_par) {
+                const uint4 sv = bfs_s[P + ts.m_hi + tid];
+                const uint32_t sw[4] = {sv.x, sv.y, sv.z, sv.w};
+                Children ch;
+                expand_node<1>(qc, sw, bfs_t[P + ts.m_hi + tid], L, lc, ch);
+                bfs_s[Q + 2u * tid] = make_uint4(ch.sl[0], ch.sl[1], ch.sl[2], ch.sl[3]);
+                bfs_s[Q + 2u * tid + 1u] = make_uint4(ch.sr[0], ch.sr[1], ch.sr[2], ch.sr[3]);
+                bfs_t[Q + 2u * tid] = (uint8_t)ch.tl;
+                bfs_t[Q + 2u * tid + 1u] = (uint8_t)ch.tr;
             }
             bar_sync(BAR_TREE, kTreeThreads);
         }
         uint32_t s[4] = {0, 0, 0, 0}, t = 0;
-        const bool active = tid < (1u << B);
+        const uint32_t kl = tid - ts.m_hi;  // lo threads: index of the root below the parents
+        const bool active = hi ? tid < m : (kl >> 1) < n_par;
         if (active) {
-            const uint4 sv = bfs_s[(B & 1) * kTreeThreads + tid];
+            const uint32_t src = hi ? P + tid : Q + kl;
+            const uint4 sv = bfs_s[src];
             s[0] = sv.x; s[1] = sv.y; s[2] = sv.z; s[3] = sv.w;
-            t = bfs_t[(B & 1) * kTreeThreads + tid];
+            t = bfs_t[src];
         }
         bar_sync(BAR_TREE, kTreeThreads);  // the sibling stack aliases the BFS buffers
         PHASE(c_bfs)
 
-        const uint64_t rowbase = ((p << B) + tid) << rows_log;  // this thread's first row
-        const uint64_t warp_row0 = ((p << B) + (tid & ~31u)) << rows_log;
-        const uint64_t warp_row1 = ((p << B) + (tid & ~31u) + 32u) << rows_log;
-        const bool warp_live = (warp * 32u < (1u << B)) && warp_row0 < end_row && warp_row1 > first_row;
-        const bool inside = row_start >= first_row && row_start + (1ull << (B + rows_log)) <= end_row;
-        const uint32_t n_slices = 1u << (rows_log - slog);
+        uint64_t warp_row0;
+        {
+            uint32_t rl_, sl_;
+            ts.group_geom(warp, row_start, warp_row0, rl_, sl_);
+        }
+        const uint64_t rowbase = warp_row0 + ((uint64_t)lane << rows_log);  // this thread's first row
+        const uint64_t warp_row1 = warp_row0 + (32ull << rows_log);
+        const bool warp_live = __any_sync(0xffffffffu, active) && warp_row0 < end_row && warp_row1 > first_row;
+        const bool inside = row_start >= first_row && row_start + ts.R <= end_row;
+        const uint32_t n_slices = 1u << ts.n_slices_log;
         // publish one slice: wait until the scan warps have drained the ring slot, store, arrive
 #define PUBLISH(word_)                                                              \
     {                                                                               \
@@ -549,7 +685,6 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
         }
 #undef PUBLISH
         PHASE(c_dfs)
-        it++;
     }
     if (ap.dbg && lane == 0) {  // spread of the tree warps' finishing times within the CTA
         const unsigned long long te = (unsigned long long)(clock64() - c_entry);
@@ -633,19 +768,26 @@ cudaError_t configure_answer_kernel() {
     return e;
 }
 
-uint64_t answer_chunks(uint64_t first_row, uint64_t n_rows, uint32_t B, uint32_t Dmin) {
-    const uint32_t cl = B + Dmin + 1u;
+uint64_t answer_tasks(uint64_t first_row, uint64_t n_rows, uint32_t D, uint32_t hi_warps) {
+    return answer_tasks_of(first_row, n_rows, D, hi_warps);
+}
+uint64_t answer_chunks(uint64_t first_row, uint64_t n_rows, uint32_t Dmin) {
+    const uint32_t cl = 10u + Dmin;
     return ((first_row + n_rows + ((1ull << cl) - 1ull)) >> cl) - (first_row >> cl);
 }
 
 cudaError_t launch_answer(const QueryConst& qc, const AnswerPlan& ap, const uint32_t* d_t0, uint32_t smem_base,
                           int num_sms, cudaStream_t st) {
     if (ap.n_rows == 0) return cudaSuccess;
-    const uint64_t chunks = answer_chunks(ap.first_row, ap.n_rows, ap.B, ap.Dmin);
-    uint64_t g = chunks < (uint64_t)num_sms ? chunks : (uint64_t)num_sms;
-    // a CTA's task list holds kMaxTasks entries and a task is at least one chunk: very large shards run
-    // more CTAs than SMs (in waves) rather than overflow it
-    const uint64_t gmin = (chunks + (kMaxTasks - 1)) / kMaxTasks;
+    if (ap.D > (uint32_t)kV2MaxDepth || ap.D + 1u > qc.num_bits || ap.hi_warps > (uint32_t)kTreeWarps || (ap.hi_warps & 3u) ||
+        (ap.hi_warps != 0u && ap.hi_warps < (uint32_t)kTreeWarps && ap.D == 0u) || (ap.hi_warps == 0u && ap.Dmin > ap.D))
+        return cudaErrorInvalidValue;
+    // units the CTAs share out: tasks (uniform split) or chunks (binary split).  A CTA's task list holds
+    // kMaxTasks entries: very large shards run more CTAs than SMs (in waves) rather than overflow it.
+    const uint64_t units = ap.hi_warps ? answer_tasks(ap.first_row, ap.n_rows, ap.D, ap.hi_warps)
+                                       : answer_chunks(ap.first_row, ap.n_rows, ap.Dmin);
+    uint64_t g = units < (uint64_t)num_sms ? units : (uint64_t)num_sms;
+    const uint64_t gmin = (units + (kMaxTasks - 1)) / kMaxTasks;
     if (g < gmin) g = gmin;
     const size_t smem = kSmemEnd - smem_base;
     // two code paths per row geometry: keys with an odd FinalCW need the leaves' control bits, keys with an

@@ -217,7 +217,7 @@ struct pir_db {
     uint8_t* h_out = nullptr;  // pinned
     uint64_t h_out_cap = 0;
     // cached work split of the answer kernel for the last (num_bits, shard rows) seen
-    uint32_t split_nb = 0, split_dmax = 0, split_dmin = 0, split_b = 0;
+    uint32_t split_nb = 0, split_d = 0, split_hiw = 0, split_dmin = 0;
     uint64_t split_first = 0, split_rows = 0;
     bool split_tp = false;
     // optional per-launch timing of the dominant (fused) kernel, for bench.py's roofline
@@ -332,33 +332,66 @@ Plan make_plan(uint32_t nb, uint64_t first_row, uint64_t n_rows, int num_sms, in
     return best;
 }
 
-// Work split of the answer kernel (answer_kernel.cu TaskIter): depth range [Dmin, Dmax] and breadth B.
-// Dmin is chosen by replaying every CTA's task sequence against a two-term cost model measured on B200
-// (a task costs its walk + breadth-first top, ~28k cycles, plus ~8k cycles per depth-first node of its threads).
+// Work split of the answer kernel (answer_kernel.cu "work split"): uniform tasks of shape (D, hi_warps), or
+// the binary split into aligned tasks of depth Dmin..D (hi_warps = 0).  Chosen against a cost model measured
+// on B200 (tools/split_sweep.py, tools/live_warps_probe.py): a sub-partition of the SM expands one node for
+// a warp in ~1.7k cycles, and with fewer than four busy warps it runs below that rate; the top of a uniform
+// task costs ~1.3k cycles per tree level above the thread roots plus ~12k for its widest levels (34k at 17
+// levels, 38k at 20); a task of the binary split costs ~36k on top of its nodes.
 struct AnswerSplit {
-    uint32_t Dmax, Dmin, B;
+    uint32_t D, hi_warps, Dmin;
 };
+double uniform_task_cost(uint32_t top_bits, uint32_t D, uint32_t hiw) {
+    const double top = 1300.0 * (double)(top_bits - D) + 12000.0 + (hiw < 16u ? 2500.0 : 0.0);
+    const double n_hi = (double)((2u << D) - 1u), n_lo = hiw < 16u ? (double)((1u << D) - 1u) : n_hi;
+    const double pen = hiw >= 16u ? 1.0 : hiw == 12u ? 1.12 : hiw == 8u ? 1.25 : 1.7;
+    return top + 1718.0 * (4.0 * n_lo + (double)(hiw / 4u) * (n_hi - n_lo) * pen);
+}
 // throughput: many independent launches run back to back on two streams (batches), so a CTA that finishes
 // early is replaced by one of the next launch: total work matters more than the slowest CTA.
 AnswerSplit choose_answer_split(uint32_t nb, uint64_t first_row, uint64_t n_rows, int num_sms, bool throughput = false) {
     AnswerSplit sp{};
-    sp.B = nb - 1 < (uint32_t)kFusedLogThreads ? nb - 1 : (uint32_t)kFusedLogThreads;
-    sp.Dmax = nb - 1 - sp.B < 7u ? nb - 1 - sp.B : 7u;
+    const uint32_t top_bits = nb - 1;
+    uint32_t dmax = top_bits > (uint32_t)kFusedLogThreads ? top_bits - (uint32_t)kFusedLogThreads : 0u;
+    if (dmax > 7u) dmax = 7u;
     if (const char* e = getenv("PIRB_DFS_DEPTH")) {
         const uint32_t f = (uint32_t)atoi(e);
-        if (f < sp.Dmax) sp.Dmax = f;
+        if (f < dmax) dmax = f;
     }
-    sp.Dmin = sp.Dmax;
-    if (const char* e = getenv("PIRB_DMIN")) {
+    sp.D = dmax;
+    sp.hi_warps = 16;
+    // fixed splits (development aids): PIRB_DFS_DEPTH x PIRB_HI_WARPS (uniform), PIRB_DFS_DEPTH / PIRB_DMIN (binary)
+    if (const char* e = getenv("PIRB_HI_WARPS")) {
         const uint32_t f = (uint32_t)atoi(e);
-        sp.Dmin = f < sp.Dmax ? f : sp.Dmax;
+        if (sp.D > 0 && (f == 4 || f == 8 || f == 12)) sp.hi_warps = f;
         return sp;
     }
+    if (const char* e = getenv("PIRB_DMIN")) {
+        const uint32_t f = (uint32_t)atoi(e);
+        sp.hi_warps = 0;
+        sp.Dmin = f < sp.D ? f : sp.D;
+        return sp;
+    }
+    if (top_bits < (uint32_t)kFusedLogThreads + 1u) return sp;  // tiny domains: one uniform task of depth 0
     double best = -1.0;
-    for (uint32_t dmin = sp.Dmax + 1; dmin-- > 0;) {  // coarse to fine: a finer split must win by 0.5%
-        const uint64_t C = answer_chunks(first_row, n_rows, sp.B, dmin);
+    auto objective = [&](double worst, double sum) { return throughput ? 0.75 * sum / (double)num_sms + 0.25 * worst : worst; };
+    for (uint32_t d = dmax + 1; d-- > 0;) {  // deep to shallow: a finer split must win by 0.5%
+        for (uint32_t hiw = 16; hiw >= 4; hiw -= 4) {
+            if (hiw < 16 && d == 0) break;
+            const uint64_t nt = answer_tasks(first_row, n_rows, d, hiw);
+            const double c = uniform_task_cost(top_bits, d, hiw);
+            const double obj = objective(c * (double)((nt + (uint64_t)num_sms - 1) / (uint64_t)num_sms), c * (double)nt);
+            if (best < 0.0 || obj < best * 0.995) {
+                best = obj;
+                sp.D = d;
+                sp.hi_warps = hiw;
+            }
+        }
+    }
+    for (uint32_t dmin = dmax + 1; dmin-- > 0;) {  // binary split: replay every CTA's task sequence
+        const uint64_t C = answer_chunks(first_row, n_rows, dmin);
         const uint64_t G = C < (uint64_t)num_sms ? C : (uint64_t)num_sms;
-        const uint64_t cf = first_row >> (sp.B + dmin + 1);
+        const uint64_t cf = first_row >> (10 + dmin);
         double worst = 0.0, sum = 0.0;
         for (uint64_t b = 0; b < G; b++) {
             uint64_t cur = cf + b * C / G, end = cf + (b + 1) * C / G;
@@ -366,19 +399,21 @@ AnswerSplit choose_answer_split(uint32_t nb, uint64_t first_row, uint64_t n_rows
             while (cur < end) {
                 uint32_t d = dmin;
                 uint64_t span = 1;
-                while (d < sp.Dmax && !(cur & (2 * span - 1)) && cur + 2 * span <= end) {
+                while (d < dmax && !(cur & (2 * span - 1)) && cur + 2 * span <= end) {
                     d++;
                     span *= 2;
                 }
-                cost += 28000.0 + 8000.0 * (double)((2u << d) - 1u);
+                cost += 36000.0 + 4.0 * 1718.0 * (double)((2u << d) - 1u);
                 cur += span;
             }
             if (cost > worst) worst = cost;
             sum += cost;
         }
-        const double obj = throughput ? 0.75 * sum / (double)num_sms + 0.25 * worst : worst;
-        if (best < 0.0 || obj < best * 0.995) {
+        const double obj = objective(worst, sum);
+        if (obj < best * 0.995) {
             best = obj;
+            sp.D = dmax;
+            sp.hi_warps = 0;
             sp.Dmin = dmin;
         }
     }
@@ -718,14 +753,14 @@ void fill_answer_split(pir_db* db, const QueryGeom& g, AnswerPlan* ap, bool thro
         db->split_nb = g.nb;
         db->split_first = g.first_row;
         db->split_rows = g.n_rows;
-        db->split_dmax = sp.Dmax;
+        db->split_d = sp.D;
+        db->split_hiw = sp.hi_warps;
         db->split_dmin = sp.Dmin;
-        db->split_b = sp.B;
     }
     ap->first_row = g.first_row;
     ap->n_rows = g.n_rows;
-    ap->D = db->split_dmax;
-    ap->B = db->split_b;
+    ap->D = db->split_d;
+    ap->hi_warps = db->split_hiw;
     ap->Dmin = db->split_dmin;
 }
 
@@ -1535,5 +1570,5 @@ extern "C" int pir_server_answer(pir_server* s, const pir_query* q, void* out, s
 extern "C" void pir_debug_answer_split(uint32_t nb, uint64_t first_row, uint64_t n_rows, int num_sms, uint32_t* Dmax,
                                        uint32_t* Dmin, uint32_t* B) {
     AnswerSplit sp = choose_answer_split(nb, first_row, n_rows, num_sms);
-    *Dmax = sp.Dmax; *Dmin = sp.Dmin; *B = sp.B;
+    *Dmax = sp.D; *Dmin = sp.Dmin; *B = sp.hi_warps;
 }

@@ -37,9 +37,10 @@ struct AnswerPlan {
     uint64_t row_bytes;   // power of two, 16..512
     uint64_t first_row;
     uint64_t n_rows;
-    uint32_t D;           // deepest per-thread DFS depth used (a thread owns up to 2^(D+1) rows)
-    uint32_t B;           // breadth-first levels per task: 2^B thread roots
-    uint32_t Dmin;        // chunk granularity of the CTA work split: chunks of 2^(B+Dmin+1) rows
+    // work split (answer_kernel.cu "work split"):
+    uint32_t D;           // uniform: every task has the shape (D, hi_warps): threads of the first hi_warps tree
+    uint32_t hi_warps;    //   warps own 2^(D+1) rows each, the others 2^D; hi_warps = 4, 8, 12 or 16 (16 if D = 0).
+    uint32_t Dmin;        // binary (hi_warps == 0): chunks of 2^(10+Dmin) rows covered by aligned tasks of depth Dmin..D
     uint32_t pad;         // debug flags
     uint32_t* out;        // row_bytes/4 words, XOR-accumulated (atomics); the caller zeroes
     uint32_t* bits_out;   // BITS mode (non-null): packed selection bits, bit i = row first_row + i, OR-accumulated
@@ -101,7 +102,8 @@ cudaError_t configure_kernels();
 // warp-specialised fused expand+scan kernel (answer_kernel.cu)
 bool answer_kernel_supports(uint64_t row_bytes, uint32_t D);
 cudaError_t configure_answer_kernel();
-uint64_t answer_chunks(uint64_t first_row, uint64_t n_rows, uint32_t B, uint32_t Dmin);
+uint64_t answer_tasks(uint64_t first_row, uint64_t n_rows, uint32_t D, uint32_t hi_warps);  // tasks of a uniform split
+uint64_t answer_chunks(uint64_t first_row, uint64_t n_rows, uint32_t Dmin);                  // chunks of a binary split
 cudaError_t launch_answer(const QueryConst& qc, const AnswerPlan& ap, const uint32_t* d_t0, uint32_t smem_base,
                           int num_sms, cudaStream_t st);
 

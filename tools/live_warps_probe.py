@@ -3,7 +3,7 @@ depth-7 task with k live warps (the others publish empty slices).  Development a
 import ctypes as C, os, sys
 import numpy as np
 sys.path.insert(0, os.getcwd())
-os.environ["PIRB_DMIN"] = "7"
+os.environ["PIRB_DFS_DEPTH"], os.environ["PIRB_HI_WARPS"] = "7", "16"
 from pir_b200 import _capi
 L = _capi.lib()
 n, S = 1 << 24, 256
