@@ -326,7 +326,10 @@ def gpu_arm(args):
                        "l2": "per-GPU shard (%d MiB) exceeds the 126 MB L2; every step scans all of it" % (shard_bytes >> 20),
                        "combine": "none" if world == 1 else "every shard's kernel XORs its %d-byte partial into rank 0's ring slot "
                                   "(red.global.xor over a CUDA IPC mapping / NVLink); no NCCL in the data path" % S,
-                       "queries": "distinct seeded key per step, share 0"},
+                       "queries": "distinct seeded key per step, share 0; FinalCW even / odd in the timed steps: %d / %d "
+                                  "(a coin flip per key; the kernel has a code path per parity)" % (
+                                      sum(1 for i in range(args.warmup, total) if not qs[2 * i].final_cw & 1),
+                                      sum(1 for i in range(args.warmup, total) if qs[2 * i].final_cw & 1))},
             "queries_per_s": 1e3 * QUERIES / ms_step,
             "e2e": {"value": db_bytes / (e2e_step * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": e2e_step,
                     "h2d_bytes_per_step": C.sizeof(_capi.PirQuery) * QUERIES, "d2h_bytes_per_step": S * QUERIES,

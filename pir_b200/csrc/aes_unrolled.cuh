@@ -110,17 +110,31 @@ __device__ __forceinline__ uint32_t leaf_parent_tail(const QueryConst& qc, const
 // is needed: block 2 of the PRG (whose only outputs are sR[15] and tR) is skipped altogether and blocks 0
 // and 1 deliver the 8 seed bytes of each child.  305 lookups instead of 438.  (Half of all keys: the
 // parity of FinalCW = b - Varint(s0) + Varint(s1) is a coin flip, dpf/client.go:127-141.)
-__device__ __forceinline__ void aes2_main_rounds(const QueryConst& qc, const uint32_t s[4], uint32_t lc,
-                                                 uint32_t a[2][4]) {
+// The same instruction stream as aes3_main_rounds with block 2 under a (warp-uniform) condition: inner nodes
+// and even-FinalCW leaf parents then share one copy of the unrolled rounds.  With a separate two-block copy
+// the depth-first loop was ~42 KB of code and the warps of a sub-partition, all at different places in it,
+// stalled on instruction fetch (ncu: no_instruction 0.53 per issued instruction against 0.05 for the
+// ~27 KB loop of odd-FinalCW keys).
+__device__ __forceinline__ void aes3_main_rounds_cond(const QueryConst& qc, const uint32_t s[4], uint32_t lc,
+                                                      uint32_t a[3][4], bool with_block2) {
 #pragma unroll
     for (int k = 0; k < 2; k++)
 #pragma unroll
         for (int c = 0; c < 4; c++) a[k][c] = s[c] ^ qc.rk[k][c];
+    if (with_block2) {
+#pragma unroll
+        for (int c = 0; c < 4; c++) a[2][c] = s[c] ^ qc.rk[2][c];
+    }
 #pragma unroll
     for (int r = 1; r <= 9; r++) {
-        uint32_t n[2][4];
+        uint32_t n[3][4];
 #pragma unroll
         for (int k = 0; k < 2; k++) aes_round(a[k], n[k], &qc.rk[k][4 * r], lc);
+        if (r <= 8 && with_block2) {
+            aes_round(a[2], n[2], &qc.rk[2][4 * r], lc);
+#pragma unroll
+            for (int c = 0; c < 4; c++) a[2][c] = n[2][c];
+        }
 #pragma unroll
         for (int k = 0; k < 2; k++)
 #pragma unroll
@@ -129,7 +143,7 @@ __device__ __forceinline__ void aes2_main_rounds(const QueryConst& qc, const uin
 }
 
 // Returns bit0 = selection bit of the left leaf, bit1 = of the right leaf (FinalCW even).
-__device__ __forceinline__ uint32_t leaf_parent_tail_even(const QueryConst& qc, const uint32_t a[2][4],
+__device__ __forceinline__ uint32_t leaf_parent_tail_even(const QueryConst& qc, const uint32_t a[3][4],
                                                           const uint32_t s[4], uint32_t t, const uint32_t cw[4],
                                                           uint32_t lc) {
     const uint32_t l0 = aes_last_word(a[0], 0, qc.rk[0][40], s[0], lc);

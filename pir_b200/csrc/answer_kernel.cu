@@ -635,9 +635,14 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
                 const uint32_t cw[4] = {qc.cw[lvl][0], qc.cw[lvl][1], qc.cw[lvl][2], qc.cw[lvl][3]};
                 const uint32_t cwtl = (uint32_t)(qc.cw_tl >> lvl) & 1u, cwtr = (uint32_t)(qc.cw_tr >> lvl) & 1u;
                 uint32_t pair;  // selection bits of the two leaves below a leaf parent
-                if (FCW_ODD || d < D) {
+                {
                     uint32_t a[3][4];
-                    aes3_main_rounds(qc, s, lc, a);
+                    // FinalCW even: the leaves' control bits do not matter, so a leaf parent skips PRG block 2
+                    // (same unrolled code as an inner node, block 2 under a warp-uniform condition)
+                    if (FCW_ODD)
+                        aes3_main_rounds(qc, s, lc, a);
+                    else
+                        aes3_main_rounds_cond(qc, s, lc, a, d < D);
                     if (d < D) {
                         Children ch;
                         inner_tail(qc, a, s, t, cw, cwtl, cwtr, lc, ch);
@@ -650,12 +655,7 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
                         d++;
                         continue;
                     }
-                    pair = leaf_parent_tail(qc, a, s, t, cw, cwtl, cwtr, lc);
-                } else {
-                    // FinalCW even: the leaves' control bits do not matter, PRG block 2 is skipped
-                    uint32_t a2[2][4];
-                    aes2_main_rounds(qc, s, lc, a2);
-                    pair = leaf_parent_tail_even(qc, a2, s, t, cw, lc);
+                    pair = FCW_ODD ? leaf_parent_tail(qc, a, s, t, cw, cwtl, cwtr, lc) : leaf_parent_tail_even(qc, a, s, t, cw, lc);
                 }
                 bw |= pair << (2u * (i & ((1u << lp_log) - 1u)));
                 i++;
