@@ -88,16 +88,67 @@ def reference_arm(args):
 # clocks sampler
 # ------------------------------------------------------------------------------------------------
 class ClockSampler:
+    """SM clock and throttle reasons sampled DURING the timed regions.  The regions last milliseconds, so the
+    sampler reads NVML directly from a thread (one sample per millisecond); `nvidia-smi -lms` is the fallback."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    REASONS = ((0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"), (0x20, "sw_thermal_slowdown"), (0x4, "sw_power_cap"))
 
     def __init__(self, gpu_index):
-        self.rows = []
+        self.rows = []          # nvidia-smi csv lines (fallback)
+        self.samples = []       # (sm_mhz, reasons bitmask) from NVML
         self.proc = None
         self.gpu = gpu_index
+        self.nvml = None
+        self.handle = None
+        self.stop_flag = threading.Event()
+        self.max_mhz = None
+
+    def _nvml_open(self):
+        import pynvml
+        pynvml.nvmlInit()
+        handle = None
+        try:
+            import torch
+            uuid = str(torch.cuda.get_device_properties(self.gpu).uuid)
+            handle = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid).encode())
+        except Exception:
+            handle = None
+        if handle is None:
+            visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = self.gpu
+            if visible:
+                try:
+                    idx = int(visible.split(",")[self.gpu])
+                except ValueError:
+                    idx = self.gpu
+            handle = pynvml.nvmlDeviceGetHandleByIndex(idx)
+        self.nvml, self.handle = pynvml, handle
+        self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(handle, pynvml.NVML_CLOCK_SM))
+
+    def _poll(self):
+        nv, hd = self.nvml, self.handle
+        while not self.stop_flag.is_set():
+            try:
+                mhz = float(nv.nvmlDeviceGetClockInfo(hd, nv.NVML_CLOCK_SM))
+                try:
+                    mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(hd))
+                except Exception:
+                    mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(hd))
+                self.samples.append((mhz, mask))
+            except Exception:
+                pass
+            time.sleep(0.001)
 
     def start(self):
+        try:
+            self._nvml_open()
+            self.t = threading.Thread(target=self._poll, daemon=True)
+            self.t.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
@@ -112,6 +163,13 @@ class ClockSampler:
             self.rows.append(line.strip())
 
     def stop(self):
+        if self.nvml is not None:
+            self.stop_flag.set()
+            self.t.join(timeout=2)
+            sm = sorted(m for m, _ in self.samples)
+            reasons = sorted({name for _, mask in self.samples for bit, name in self.REASONS if mask & bit})
+            return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz, "reasons": reasons,
+                    "samples": len(sm), "source": "nvml, 1 ms period, during both timed regions"}
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -134,7 +192,7 @@ class ClockSampler:
                     reasons.add(name)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi -lms 100"}
 
 
 # ------------------------------------------------------------------------------------------------

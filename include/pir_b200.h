@@ -151,6 +151,9 @@ int pir_server_num_shards(const pir_server* s);
 int pir_server_shard(pir_server* s, int i, pir_db** db);
 int pir_server_upload(pir_server* s, uint64_t slot_index, const void* host_slots, uint64_t n_slots);
 int pir_server_fill_synthetic(pir_server* s, uint64_t seed);
+/* Database.SetKeywords (db.go:392-394) for the whole database: n must equal db_size; shard g keeps
+ * keywords[slot_begin_g, +slot_count_g).  Keyword queries (db.go:119-121,132-135) need group_size 1 here. */
+int pir_server_set_keywords(pir_server* s, const uint64_t* keywords, uint64_t n);
 /* PrivateSecretSharedQuery (db.go:68-72) over all shards: out gets group_size*slot_bytes bytes. */
 int pir_server_answer(pir_server* s, const pir_query* q, void* out, size_t out_len);
 int pir_server_answer_batch(pir_server* s, const pir_query* qs, uint32_t n_queries, void* out, size_t out_len);

@@ -32,7 +32,7 @@ EXPORTS = [
     "pir_kernel_launch_count", "pir_client_gen_two_server",
     "pir_db_set_kernel_timing", "pir_db_get_kernel_timing",
     "pir_server_create", "pir_server_destroy", "pir_server_num_shards", "pir_server_shard",
-    "pir_server_upload", "pir_server_fill_synthetic", "pir_server_answer", "pir_server_answer_batch",
+    "pir_server_upload", "pir_server_fill_synthetic", "pir_server_set_keywords", "pir_server_answer", "pir_server_answer_batch",
     "pir_combine_create", "pir_combine_export", "pir_combine_open", "pir_combine_destroy",
     "pir_combine_reset", "pir_answer_accumulate_device", "pir_combine_wait_read", "pir_combine_slot_ptr",
     "pir_audit_shared_query", "pir_audit_shared_query_with_bits",
@@ -133,6 +133,7 @@ def lib():
     L.pir_server_shard.argtypes = [vp, C.c_int, C.POINTER(vp)]
     L.pir_server_upload.argtypes = [vp, C.c_uint64, vp, C.c_uint64]
     L.pir_server_fill_synthetic.argtypes = [vp, C.c_uint64]
+    L.pir_server_set_keywords.argtypes = [vp, u64p, C.c_uint64]
     L.pir_server_answer.argtypes = [vp, qp, vp, C.c_size_t]
     L.pir_server_answer_batch.argtypes = [vp, qp, C.c_uint32, vp, C.c_size_t]
     L.pir_combine_create.argtypes = [C.c_int, C.c_uint32, C.c_size_t, C.POINTER(vp)]

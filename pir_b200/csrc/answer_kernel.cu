@@ -33,7 +33,7 @@ constexpr int kTreeWarps = kTreeThreads / 32;
 constexpr int kScanWarps = 4;
 constexpr int kAnswerThreads = kTreeThreads + 32 * kScanWarps;
 constexpr int kV2MaxDepth = 7;                 // a thread owns at most 2^8 rows (sibling stack: 7 x 16 B)
-constexpr uint32_t kSliceLog = 3;              // rows per thread per slice (8), fewer for tiny depths
+constexpr uint32_t kSliceLog = 3;              // rows per thread per slice: at most 8; AnswerPlan::slog_cap picks 4 for shallow tasks
 constexpr uint32_t kRing = 8;                  // slice buffers in flight between tree and scan warps
 constexpr uint32_t kListEntries = 256;         // rows selected out of 32 words of a slice, per warp
 
@@ -105,7 +105,7 @@ __device__ __forceinline__ uint32_t range_mask32(uint64_t rowbase, uint32_t rw, 
 }
 
 // rows per thread per slice (log2) for a task of depth d: 8, or all 2^(d+1) rows when there are fewer
-__device__ __forceinline__ uint32_t slice_log(uint32_t d) { return d + 1u < kSliceLog ? d + 1u : kSliceLog; }
+__device__ __forceinline__ uint32_t slice_log(uint32_t d, uint32_t cap) { return d + 1u < cap ? d + 1u : cap; }
 
 // ---- scan: selected rows of 32 words of a slice -> registers ----------------------------------------
 struct ScanLane {
@@ -243,12 +243,12 @@ struct TaskShape {
     uint32_t m_hi, m_nom;  // hi thread roots; nodes of the hi roots' tree level the task spans (hi roots + lo parents)
     uint32_t slog, n_slices_log;
     uint64_t R;
-    __device__ __forceinline__ void set(uint32_t d, uint32_t hi_warps) {
+    __device__ __forceinline__ void set(uint32_t d, uint32_t hi_warps, uint32_t slog_cap) {
         D = d;
         hiw = hi_warps;
         m_hi = 32u * hiw;
         m_nom = m_hi + 16u * (kTreeWarps - hiw);
-        slog = slice_log(D);
+        slog = slice_log(D, slog_cap);
         n_slices_log = D + 1u - slog;
         R = (uint64_t)(kTreeWarps + hiw) << (D + 5u);
     }
@@ -284,7 +284,7 @@ struct ChunkRange {
     }
 };
 
-// The CTA's task list in shared memory: n, then (64-bit) base and stride, then n entries
+// The CTA's task list in shared memory: n, the slice cap (log2), then (64-bit) base and stride, then n entries
 // (offset << 5 | (hi_warps/4 - 1) << 3 | d); a task's first row is base + offset * stride.
 struct TaskIter {
     const uint32_t* list;
@@ -293,12 +293,12 @@ struct TaskIter {
     __device__ __forceinline__ void decode(uint32_t k, uint64_t& row_start, TaskShape& ts) const {
         const uint32_t e = list[kTaskHeader + k];
         const uint64_t base = *reinterpret_cast<const uint64_t*>(list + 2), stride = *reinterpret_cast<const uint64_t*>(list + 4);
-        ts.set(e & 7u, 4u * (((e >> 3) & 3u) + 1u));
+        ts.set(e & 7u, 4u * (((e >> 3) & 3u) + 1u), list[1]);
         row_start = base + (uint64_t)(e >> 5) * stride;
     }
     __device__ __forceinline__ uint32_t slices_log(uint32_t k) const {  // log2(slices of task k)
         const uint32_t d = list[kTaskHeader + k] & 7u;
-        return d + 1u - slice_log(d);
+        return d + 1u - slice_log(d, list[1]);
     }
 };
 
@@ -308,7 +308,7 @@ __device__ __forceinline__ void build_task_list(const AnswerPlan& ap, uint32_t* 
     uint32_t* entries = task_list + kTaskHeader;
     if (ap.hi_warps) {
         TaskShape ts;
-        ts.set(ap.D, ap.hi_warps);
+        ts.set(ap.D, ap.hi_warps, ap.slog_cap);
         base = (ap.first_row & ~((2ull << ap.D) - 1ull)) + (uint64_t)blockIdx.x * ts.R;
         stride = (uint64_t)gridDim.x * ts.R;
         const uint64_t NT = answer_tasks_of(ap.first_row, ap.n_rows, ap.D, ap.hi_warps);
@@ -337,6 +337,7 @@ __device__ __forceinline__ void build_task_list(const AnswerPlan& ap, uint32_t* 
         }
     }
     task_list[0] = n;
+    task_list[1] = ap.slog_cap;
     *reinterpret_cast<uint64_t*>(task_list + 2) = base;
     *reinterpret_cast<uint64_t*>(task_list + 4) = stride;
 }
@@ -713,6 +714,11 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
               const uint32_t* __restrict__ t0) {
     const uint32_t base = smem_addr(g_smem2);
     const long long c_entry = clock64();
+    if (ap.dbg && threadIdx.x == 0) {  // CTA start on the GPU-wide timer (ns): launch stagger across SMs
+        unsigned long long gt;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+        ap.dbg[12288ull + blockIdx.x] = gt;
+    }
     {
         uint32_t dyn;
         asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dyn));
@@ -743,6 +749,28 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
         for (uint32_t i = threadIdx.x; i < words_out; i += kAnswerThreads) {
             const uint32_t v = red[i];
             if (v) atomicXor(&ap.out[i], v);
+        }
+        if (ap.arrivals) {
+            // Multi-GPU combine: this shard's partial is complete once every CTA's XORs are visible.  Each thread
+            // fences its own atomics (the slot may live on a peer GPU), the CTA counts itself in, and the last
+            // CTA of the launch publishes the arrival (kernels.cu wait_arrivals_kernel acquires it on the owner).
+            __threadfence_system();
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                if (atomicAdd(ap.cta_done, 1u) == gridDim.x - 1u) {
+                    *ap.cta_done = 0u;  // ready for the launch that reuses this counter
+                    __threadfence_system();
+                    atomicAdd_system(ap.arrivals, 1u);
+                }
+            }
+        }
+    }
+    if (ap.dbg) {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned long long gt;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+            ap.dbg[13312ull + blockIdx.x] = gt;
         }
     }
 }
@@ -780,7 +808,8 @@ cudaError_t launch_answer(const QueryConst& qc, const AnswerPlan& ap, const uint
                           int num_sms, cudaStream_t st) {
     if (ap.n_rows == 0) return cudaSuccess;
     if (ap.D > (uint32_t)kV2MaxDepth || ap.D + 1u > qc.num_bits || ap.hi_warps > (uint32_t)kTreeWarps || (ap.hi_warps & 3u) ||
-        (ap.hi_warps != 0u && ap.hi_warps < (uint32_t)kTreeWarps && ap.D == 0u) || (ap.hi_warps == 0u && ap.Dmin > ap.D))
+        (ap.hi_warps != 0u && ap.hi_warps < (uint32_t)kTreeWarps && ap.D == 0u) || (ap.hi_warps == 0u && ap.Dmin > ap.D) ||
+        ap.slog_cap < 2u || ap.slog_cap > kSliceLog)  // (2: the lo warps of a mixed task publish half-size slices of >= 2 rows)
         return cudaErrorInvalidValue;
     // units the CTAs share out: tasks (uniform split) or chunks (binary split).  A CTA's task list holds
     // kMaxTasks entries: very large shards run more CTAs than SMs (in waves) rather than overflow it.

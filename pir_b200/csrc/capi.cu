@@ -208,6 +208,8 @@ struct pir_db {
     uint64_t front_cap = 0;
     uint8_t* d_bits = nullptr;
     uint64_t bits_cap = 0;
+    uint32_t* d_cta_done = nullptr;  // multi-GPU combine: ring of kCtaDoneRing per-launch "CTAs finished" counters
+    uint32_t cta_done_next = 0;
     uint32_t* d_bitmat = nullptr;  // batched path: [queries][words] packed selection bits
     uint64_t bitmat_cap = 0;       // in words
     cudaStream_t side[2] = {nullptr, nullptr};  // batched path: phase-1 kernels alternate between two streams
@@ -467,6 +469,7 @@ extern "C" int pir_db_destroy(pir_db* db) {
     }
     if (db->d_bits) cudaFree(db->d_bits);
     if (db->d_bitmat) cudaFree(db->d_bitmat);
+    if (db->d_cta_done) cudaFree(db->d_cta_done);
     for (int k = 0; k < 2; k++)
         if (db->side[k]) cudaStreamDestroy(db->side[k]);
     for (int k = 0; k < 3; k++)
@@ -602,8 +605,13 @@ int query_geom(const pir_db* db, const pir_query* q, QueryGeom* g) {
 }
 
 // Enqueue one query's work on `st`; d_out receives the pitched answer (row_bytes bytes).
+constexpr uint32_t kCtaDoneRing = 64;
+
+// arrivals / signalled: multi-GPU combine.  When the warp-specialised kernel answers the query, its last CTA
+// bumps *arrivals itself (system scope, after its partial has been XORed into d_out) and *signalled is set;
+// on every other path the caller launches the signalling kernel.
 int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* d_out, cudaStream_t st,
-                   bool zero_first = true) {
+                   bool zero_first = true, uint32_t* arrivals = nullptr, bool* signalled = nullptr) {
     // every kernel below XOR-accumulates into d_out (atomics), so a caller that combines several shards
     // into one buffer passes zero_first = false and zeroes it once itself
     if (zero_first) CU(cudaMemsetAsync(d_out, 0, g.row_bytes, st));
@@ -634,12 +642,21 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
         ap.row_bytes = g.row_bytes;
         fill_answer_split(db, g, &ap);
         ap.out = (uint32_t*)d_out;
+        if (arrivals && signalled && !getenv("PIRB_SIGNAL_KERNEL")) {
+            if (!db->d_cta_done) {
+                CU(cudaMalloc(&db->d_cta_done, kCtaDoneRing * sizeof(uint32_t)));
+                CU(cudaMemset(db->d_cta_done, 0, kCtaDoneRing * sizeof(uint32_t)));
+            }
+            ap.arrivals = arrivals;
+            ap.cta_done = db->d_cta_done + (db->cta_done_next++ % kCtaDoneRing);  // reset by the launch's last CTA
+            *signalled = true;
+        }
         if (const char* dbg = getenv("PIRB_DEBUG_FLAGS")) ap.pad = (uint32_t)atoi(dbg);  // timing experiments only
         static const bool phase_debug = getenv("PIRB_PHASE_DEBUG") != nullptr;
         unsigned long long* d_dbg = nullptr;
         if (phase_debug) {
-            CU(cudaMalloc(&d_dbg, 8 * 12 * 1024));
-            CU(cudaMemsetAsync(d_dbg, 0, 8 * 12 * 1024, st));
+            CU(cudaMalloc(&d_dbg, 8 * 14 * 1024));
+            CU(cudaMemsetAsync(d_dbg, 0, 8 * 14 * 1024, st));
             ap.dbg = d_dbg;
         }
         cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -657,9 +674,9 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
         CU(launch_answer(qc, ap, ctx.d_t0, ctx.smem_base, ctx.num_sms, st));
         if (e1) CU(cudaEventRecord(e1, st));
         if (d_dbg) {  // development aid: average per-CTA cycles per phase of the tree warps, to stderr
-            std::vector<unsigned long long> h(12 * 1024);
+            std::vector<unsigned long long> h(14 * 1024);
             CU(cudaStreamSynchronize(st));
-            CU(cudaMemcpy(h.data(), d_dbg, 8 * 12 * 1024, cudaMemcpyDeviceToHost));
+            CU(cudaMemcpy(h.data(), d_dbg, 8 * 14 * 1024, cudaMemcpyDeviceToHost));
             cudaFree(d_dbg);
             double sum[8] = {0}, mx = 0;
             int n = 0;
@@ -669,11 +686,22 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
                 for (int k = 0; k < 8; k++) sum[k] += (double)h[8 * b + k];
                 if ((double)(h[8 * b + 5] + h[8 * b + 7]) > mx) mx = (double)(h[8 * b + 5] + h[8 * b + 7]);
             }
+            unsigned long long g0 = ~0ull, g1 = 0, gs_last = 0, ge_first = ~0ull;
+            for (int b = 0; b < 1024; b++)
+                if (h[8 * b + 5]) {
+                    if (h[12288 + b] < g0) g0 = h[12288 + b];
+                    if (h[12288 + b] > gs_last) gs_last = h[12288 + b];
+                    if (h[13312 + b] > g1) g1 = h[13312 + b];
+                    if (h[13312 + b] < ge_first) ge_first = h[13312 + b];
+                }
+            if (n) fprintf(stderr, "[phase] globaltimer: first CTA start to last CTA start %llu ns, first CTA end at %llu ns, last CTA end at %llu ns\n",
+                           gs_last - g0, ge_first - g0, g1 - g0);
             if (getenv("PIRB_PHASE_DEBUG")[0] == '2')
                 for (int b = 0; b < 1024; b++)
                     if (h[8 * b + 5])
-                        fprintf(stderr, "[cta %d] tasks %llu prologue %llu top %llu bfs %llu dfs %llu tail %llu total %llu\n", b, h[8 * b + 6],
-                                h[8 * b + 7], h[8 * b + 0], h[8 * b + 1], h[8 * b + 3], h[8 * b + 4], h[8 * b + 5] + h[8 * b + 7]);
+                        fprintf(stderr, "[cta %d] tasks %llu prologue %llu top %llu bfs %llu dfs %llu tail %llu total %llu start_ns %llu end_ns %llu\n", b, h[8 * b + 6],
+                                h[8 * b + 7], h[8 * b + 0], h[8 * b + 1], h[8 * b + 3], h[8 * b + 4], h[8 * b + 5] + h[8 * b + 7],
+                                h[12288 + b] - g0, h[13312 + b] - g0);
             double spread = 0;
             for (int b = 0; b < 1024; b++)
                 if (h[8 * b + 5]) spread += (double)h[8192 + 2 * b] - (double)((1ull << 40) - h[8192 + 2 * b + 1]);
@@ -762,6 +790,13 @@ void fill_answer_split(pir_db* db, const QueryGeom& g, AnswerPlan* ap, bool thro
     ap->D = db->split_d;
     ap->hi_warps = db->split_hiw;
     ap->Dmin = db->split_dmin;
+    // Slices of 8 rows per thread, or of 4 when the task a CTA ends with is shallow: the rows of the last slice
+    // are scanned after the tree warps are done, and with 32 rows per thread that slice is a quarter of the task.
+    ap->slog_cap = (ap->hi_warps != 0u && ap->D <= 4u) ? 2u : 3u;
+    if (const char* e = getenv("PIRB_SLICE_LOG")) {  // development aid
+        const uint32_t f = (uint32_t)atoi(e);
+        if (f == 2u || f == 3u) ap->slog_cap = f;
+    }
 }
 
 // Should a batch of n index queries go through the two-phase path (bit vectors, then ONE pass over the
@@ -1333,8 +1368,11 @@ extern "C" int pir_answer_accumulate_device(pir_db* db, const pir_query* q, pir_
     if (rc) return rc;
     if (geom.row_bytes > c->stride) return fail(PIR_ERR_BAD_ARG, "answer of %llu bytes exceeds the slot stride %zu",
                                                 (unsigned long long)geom.row_bytes, c->stride);
-    if ((rc = enqueue_answer(db, q, geom, c->base + (size_t)slot * c->stride, st, /*zero_first=*/false))) return rc;
-    CU(launch_signal_arrival(c->arrivals(slot), st));
+    bool signalled = false;
+    if ((rc = enqueue_answer(db, q, geom, c->base + (size_t)slot * c->stride, st, /*zero_first=*/false, c->arrivals(slot),
+                             &signalled)))
+        return rc;
+    if (!signalled) CU(launch_signal_arrival(c->arrivals(slot), st));
     return PIR_OK;
 }
 
@@ -1499,6 +1537,18 @@ extern "C" int pir_server_upload(pir_server* s, uint64_t slot_index, const void*
         const uint64_t e = e0 < e1 ? e0 : e1;
         if (b >= e) continue;
         int rc = pir_db_upload(db, b, (const uint8_t*)host_slots + (b - slot_index) * (uint64_t)s->slot_bytes, e - b);
+        if (rc) return rc;
+    }
+    return PIR_OK;
+}
+
+extern "C" int pir_server_set_keywords(pir_server* s, const uint64_t* keywords, uint64_t n) {
+    if (!s || !keywords) return fail(PIR_ERR_BAD_ARG, "null argument");
+    if (n != s->db_size)
+        return fail(PIR_ERR_BAD_ARG, "expected %llu keywords (one per slot), got %llu", (unsigned long long)s->db_size,
+                    (unsigned long long)n);
+    for (pir_db* db : s->shards) {  // every shard keeps the keywords of its own slots only
+        int rc = pir_db_set_keywords(db, keywords + db->slot_begin, db->slot_count);
         if (rc) return rc;
     }
     return PIR_OK;

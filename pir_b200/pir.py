@@ -5,6 +5,7 @@ path; the server methods run on the GPU through the C ABI (include/pir_b200.h). 
 and ignored, like the reference ignores it in PrivateSecretSharedQueryWithExpandedBits (db.go:75).
 """
 import ctypes as C
+import math
 import os
 
 import numpy as np
@@ -23,6 +24,14 @@ class Slot:
             return False
         return bytes(self.Data) == bytes(other.Data)
 
+    def Compare(self, other):  # slot.go:56-58 (bytes.Compare: -1, 0, 1)
+        a, b = bytes(self.Data), bytes(other.Data)
+        return (a > b) - (a < b)
+
+    def ToString(self):  # slot.go:61-63: trailing zero bytes removed (an all-zero slot keeps one)
+        raw = bytes(self.Data).rstrip(b"\x00")
+        return (raw if raw else b"\x00").decode("latin-1")
+
     def __repr__(self):
         return "Slot(%s)" % bytes(self.Data).hex()
 
@@ -33,6 +42,21 @@ def XorSlots(a, b):
     if n:
         x = np.frombuffer(bytes(a.Data[:n]), dtype=np.uint8) ^ np.frombuffer(bytes(b.Data[:n]), dtype=np.uint8)
         a.Data[:n] = x.tobytes()
+
+
+def NewSlot(b):  # slot.go:148-152
+    return Slot(b)
+
+
+def NewSlotFromString(s, slotSize):
+    """slot.go:137-145: the string's bytes, zero padded up to slotSize (never truncated)."""
+    raw = s.encode("latin-1") if isinstance(s, str) else bytes(s)
+    return Slot(raw + bytes(max(0, slotSize - len(raw))))
+
+
+def GetRequiredSlotSize(data):
+    """slot.go:174-186: the longest string, in bytes."""
+    return max([len(s.encode("latin-1") if isinstance(s, str) else bytes(s)) for s in data], default=0)
 
 
 def NewEmptySlot(numBytes):
@@ -111,6 +135,17 @@ class DBMetadata:
 
     def IndexToCoordinates(self, index, width, height):  # db.go:399-401
         return index // width, index % width
+
+    def GetDimentionsForDatabase(self, height, groupSize):
+        """db.go:406-420 (integer divisions inside math.Ceil, as written there)."""
+        dimWidth = self.DBSize // (height * groupSize)
+        if dimWidth == 0:
+            dimWidth = 1
+        dimHeight = self.DBSize // (dimWidth * groupSize)
+        return dimWidth * groupSize, dimHeight
+
+    def GetSqrtOfDBSize(self):  # db.go:423-425
+        return int(math.sqrt(float(self.DBSize)) + 1)
 
 
 class Database(DBMetadata):
@@ -221,7 +256,7 @@ class Database(DBMetadata):
 
     # -- db.go:364-394 --
     def BuildForData(self, data):
-        self.BuildForDataWithSlotSize(data, max(len(s.encode()) for s in data))
+        self.BuildForDataWithSlotSize(data, GetRequiredSlotSize(data))
 
     def BuildForDataWithSlotSize(self, data, slotSize):
         self.Close()
@@ -230,7 +265,7 @@ class Database(DBMetadata):
         self.Slots = []
         for s in data:
             d = bytearray(slotSize)
-            raw = s.encode() if isinstance(s, str) else bytes(s)
+            raw = s.encode("latin-1") if isinstance(s, str) else bytes(s)
             d[:min(len(raw), slotSize)] = raw[:slotSize]
             self.Slots.append(Slot(d))
 
@@ -242,6 +277,18 @@ class Database(DBMetadata):
 
 def NewDatabase():
     return Database()
+
+
+def GetOptimalDBDimentions(slotSize, dbSize):
+    """db.go:428-434"""
+    height = int(max(1.0, math.sqrt(float(dbSize * slotSize))))
+    return int(math.ceil(float(dbSize) / float(height))), height
+
+
+def GetOptimalWeightedDBDimentions(slotSize, dbSize, weight):
+    """db.go:438-446"""
+    width, height = GetOptimalDBDimentions(slotSize, dbSize)
+    return width // weight, height * weight
 
 
 def GenerateRandomDB(size, numBytes, device=0):

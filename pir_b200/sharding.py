@@ -89,6 +89,11 @@ class Server:
     def fill_synthetic(self, seed):
         _capi.check(self.L.pir_server_fill_synthetic(self.h, seed))
 
+    def set_keywords(self, keywords):
+        """Database.SetKeywords (db.go:392-394): one keyword per slot; every shard keeps its own slots' keywords."""
+        kw = np.ascontiguousarray(keywords, dtype=np.uint64)
+        _capi.check(self.L.pir_server_set_keywords(self.h, kw.ctypes.data_as(C.POINTER(C.c_uint64)), kw.size))
+
     def answer(self, q):
         n = q.group_size * self.slot_bytes
         out = np.zeros(n, dtype=np.uint8)

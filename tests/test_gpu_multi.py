@@ -42,6 +42,28 @@ def test_server_answer_matches_oracle(gpu_lib, n_shards, db_size, slot_bytes, W)
         assert np.array_equal(both[0], a0) and np.array_equal(both[1], a1) and np.array_equal(both[2], a0)
 
 
+@pytest.mark.parametrize("n_shards,db_size,slot_bytes", [(1, 900, 32), (3, 5000, 32), (8, 1 << 14, 40)])
+def test_server_keyword_query_over_shards(gpu_lib, n_shards, db_size, slot_bytes):
+    """BASELINE configs[4]'s keyword half at test size: a keyword query (db.go:119-121,132-135) over a
+    row-sharded database; every shard evaluates the 32-level DPF at its own rows' keywords."""
+    rng = np.random.default_rng(21)
+    data = rng.integers(0, 256, size=(db_size, slot_bytes), dtype=np.uint8)
+    kws = np.sort(rng.choice(1 << 32, size=db_size, replace=False).astype(np.uint64))
+    target = (db_size * 5) // 7
+    (o0, o1), (q0, q1) = make_queries(13, db_size, 1, target, is_keyword=True, keyword=int(kws[target]))
+    with sharding.Server(_devices(gpu_lib, n_shards), db_size, slot_bytes) as srv:
+        srv.upload(data)
+        with pytest.raises(_capi.PirError):
+            srv.answer(q0)                      # no keywords yet
+        with pytest.raises(_capi.PirError):
+            srv.set_keywords(kws[:-1])          # one keyword per slot
+        srv.set_keywords(kws)
+        a0, a1 = srv.answer(q0), srv.answer(q1)
+        assert np.array_equal(a0, oracle.answer(o0, data, db_size, slot_bytes, keywords=kws))
+        assert np.array_equal(a1, oracle.answer(o1, data, db_size, slot_bytes, keywords=kws))
+        assert np.array_equal(a0 ^ a1, data[target])
+
+
 def test_server_upload_routes_to_shards(gpu_lib):
     rng = np.random.default_rng(3)
     db_size, S = 1000, 48

@@ -11,7 +11,10 @@ L = _capi.lib()
 n, S = 1 << 24, 256
 nb = L.pir_num_bits_for(n, 1, 0)
 rng = np.random.default_rng(1)
-for frac, dmin in ((1, "b4"), (1, "7x12"), (2, "auto"), (8, "auto")):
+cases = ((1, "b4"), (1, "7x12"), (2, "auto"), (8, "auto"))
+if os.environ.get("PIRB_PHASE_CASES"):   # e.g. "8:auto,1:b4"
+    cases = tuple((int(c.split(":")[0]), c.split(":")[1]) for c in os.environ["PIRB_PHASE_CASES"].split(","))
+for frac, dmin in cases:
     for k in ("PIRB_DFS_DEPTH", "PIRB_HI_WARPS", "PIRB_DMIN"):
         os.environ.pop(k, None)
     if dmin.startswith("b"):
