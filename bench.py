@@ -27,6 +27,7 @@ sys.path.insert(0, ROOT)
 LOG_ROWS = int(os.environ.get("PIRB_BENCH_LOG_ROWS", "24"))
 SLOT_BYTES = int(os.environ.get("PIRB_BENCH_SLOT_BYTES", "256"))
 QUERIES = int(os.environ.get("PIRB_BENCH_QUERIES", "1"))   # queries answered per step (one pir_answer_batch call)
+KEYWORD = bool(int(os.environ.get("PIRB_BENCH_KEYWORD", "0")))  # configs[4]'s keyword half: 32-bit keyword queries
 SEED = 2024
 CPU_SAMPLE_LOG_ROWS = 20
 METRIC = "dpf_pir_answer_db_scan_throughput"
@@ -36,7 +37,22 @@ UNIT = "GB/s"
 def workload_name():
     return "2^%d rows x %d-byte slots (%.1f GiB DB), %s, group size 1" % (
         LOG_ROWS, SLOT_BYTES, (1 << LOG_ROWS) * SLOT_BYTES / 2**30,
-        "single query" if QUERIES == 1 else "batch of %d queries per step" % QUERIES)
+        ("single keyword query (sorted distinct 32-bit keywords)" if KEYWORD else "single query") if QUERIES == 1
+        else "batch of %d queries per step" % QUERIES)
+
+
+def keywords_for(r0, r1):
+    """Synthetic keyword column (Database.Keywords, db.go:392-394) for rows [r0, r1): sorted, distinct 32-bit values;
+    row i's keyword has i in its top LOG_ROWS bits and seeded pseudo-random low bits."""
+    import numpy as np
+    low = 32 - LOG_ROWS
+    out = np.empty(r1 - r0, dtype=np.uint64)
+    for c0 in range(r0, r1, 1 << 24):   # in chunks: 2^28 keywords would otherwise need several 2 GiB temporaries
+        c1 = min(r1, c0 + (1 << 24))
+        i = np.arange(c0, c1, dtype=np.uint64)
+        mix = (i * np.uint64(0x9E3779B97F4A7C15) + np.uint64(SEED)) >> np.uint64(40)
+        out[c0 - r0:c1 - r0] = (i << np.uint64(low)) | (mix & np.uint64((1 << low) - 1))
+    return out
 
 
 # ------------------------------------------------------------------------------------------------
@@ -222,7 +238,13 @@ def gpu_arm(args):
     h = C.c_void_p()
     _capi.check(L.pir_db_create(local, n, S, r0, r1 - r0, C.byref(h)))
     _capi.check(L.pir_db_fill_synthetic(h, SEED))
-    nb = L.pir_num_bits_for(n, 1, 0)
+    nb = L.pir_num_bits_for(n, 1, 1 if KEYWORD else 0)
+    if KEYWORD:
+        if LOG_ROWS > 32 or QUERIES != 1:
+            raise SystemExit("bench.py: PIRB_BENCH_KEYWORD needs LOG_ROWS <= 32 and single queries")
+        kw = np.ascontiguousarray(keywords_for(r0, r1))
+        _capi.check(L.pir_db_set_keywords(h, kw.ctypes.data_as(C.POINTER(C.c_uint64)), kw.size))
+        del kw
 
     total = args.warmup + args.steps
     rng = np.random.default_rng(SEED)
@@ -230,7 +252,10 @@ def gpu_arm(args):
     qs = (_capi.PirQuery * (2 * (total + 1)))()
     for i, idx in enumerate(idxs):
         tape = (C.c_uint8 * 97).from_buffer_copy(rng.integers(0, 256, size=97, dtype=np.uint8).tobytes())
-        _capi.check(L.pir_client_gen_two_server(nb, idx, 1, tape, C.byref(qs[2 * i]), C.byref(qs[2 * i + 1])))
+        a = int(keywords_for(idx, idx + 1)[0]) if KEYWORD else idx
+        _capi.check(L.pir_client_gen_two_server(nb, a, 1, tape, C.byref(qs[2 * i]), C.byref(qs[2 * i + 1])))
+        if KEYWORD:
+            qs[2 * i].is_keyword = qs[2 * i + 1].is_keyword = 1
 
     if QUERIES > 1 and world > 1:
         raise SystemExit("bench.py: PIRB_BENCH_QUERIES > 1 is a single-GPU workload (configs[3])")
@@ -397,10 +422,10 @@ def gpu_arm(args):
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic,
-                         "kernel": "answer_kernel" if QUERIES == 1 else "answer_kernel (bit vectors) + batch_scan_kernel, per query", "kernel_ms": k_avg_ms,
+                         "kernel": "keyword_walk_kernel + scan_bytes_kernel" if KEYWORD else "answer_kernel" if QUERIES == 1 else "answer_kernel (bit vectors) + batch_scan_kernel, per query", "kernel_ms": k_avg_ms,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650",
                          "algorithmic_bytes_per_launch": shard_bytes,
-                         "aes_blocks_per_s": 3.0 * (r1 - r0) / (k_avg_ms * 1e-3)},
+                         "aes_blocks_per_s": None if KEYWORD else 3.0 * (r1 - r0) / (k_avg_ms * 1e-3)},
             "clocks": clocks,
         }
         if world == 1:

@@ -754,14 +754,14 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
             // Multi-GPU combine: this shard's partial is complete once every CTA's XORs are visible.  Each thread
             // fences its own atomics (the slot may live on a peer GPU), the CTA counts itself in, and the last
             // CTA of the launch publishes the arrival (kernels.cu wait_arrivals_kernel acquires it on the owner).
+            // (Folding the CTAs' partials in local memory first and forwarding one sum per shard was measured on
+            // 8 GPUs: no difference, the 148 x 64 remote atomics per shard are not a bottleneck.)
             __threadfence_system();
             __syncthreads();
-            if (threadIdx.x == 0) {
-                if (atomicAdd(ap.cta_done, 1u) == gridDim.x - 1u) {
-                    *ap.cta_done = 0u;  // ready for the launch that reuses this counter
-                    __threadfence_system();
-                    atomicAdd_system(ap.arrivals, 1u);
-                }
+            if (threadIdx.x == 0 && atomicAdd(ap.cta_done, 1u) == gridDim.x - 1u) {
+                *ap.cta_done = 0u;  // ready for the launch that reuses this counter
+                __threadfence_system();
+                atomicAdd_system(ap.arrivals, 1u);
             }
         }
     }
