@@ -611,7 +611,7 @@ constexpr uint32_t kCtaDoneRing = 64;
 // bumps *arrivals itself (system scope, after its partial has been XORed into d_out) and *signalled is set;
 // on every other path the caller launches the signalling kernel.
 int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* d_out, cudaStream_t st,
-                   bool zero_first = true, uint32_t* arrivals = nullptr, bool* signalled = nullptr) {
+                   bool zero_first = true, uint32_t* arrivals = nullptr, bool* signalled = nullptr, bool throughput = false) {
     // every kernel below XOR-accumulates into d_out (atomics), so a caller that combines several shards
     // into one buffer passes zero_first = false and zeroes it once itself
     if (zero_first) CU(cudaMemsetAsync(d_out, 0, g.row_bytes, st));
@@ -640,7 +640,7 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
         AnswerPlan ap{};
         ap.db = db->d_slots;
         ap.row_bytes = g.row_bytes;
-        fill_answer_split(db, g, &ap);
+        fill_answer_split(db, g, &ap, throughput);
         ap.out = (uint32_t*)d_out;
         if (arrivals && signalled && !getenv("PIRB_SIGNAL_KERNEL")) {
             if (!db->d_cta_done) {
@@ -881,6 +881,38 @@ int enqueue_batch_bits(pir_db* db, const pir_query* qs, uint32_t n, const QueryG
 }
 
 // pitched device answer -> dense host answer (Shares[c].Data = out[c*S, (c+1)*S))
+// A batch answered by one fused launch per query (rows narrower than 512 B).  The launches are independent (each
+// XORs into its own answer), so they alternate between two side streams: the CTAs of the next launch start on SMs
+// that the previous one has already left, which hides every launch's ramp-down and launch gap.  Keyword queries
+// and the two-launch fallback share per-handle scratch and stay on one stream.
+int enqueue_batch_fused(pir_db* db, const pir_query* qs, uint32_t n, const QueryGeom& g0, uint8_t* d_out, cudaStream_t st) {
+    int rc;
+    const bool v1 = getenv("PIRB_KERNEL") && !strcmp(getenv("PIRB_KERNEL"), "v1");
+    const bool two_streams = n >= 2 && !qs[0].is_keyword && !v1 && g0.n_rows != 0 && answer_kernel_supports(g0.row_bytes, 0) &&
+                             !getenv("PIRB_BATCH_ONE_STREAM") && !getenv("PIRB_PHASE_DEBUG");
+    if (!two_streams) {
+        for (uint32_t i = 0; i < n; i++)
+            if ((rc = enqueue_answer(db, &qs[i], g0, d_out + (uint64_t)i * g0.row_bytes, st))) return rc;
+        return PIR_OK;
+    }
+    for (int k = 0; k < 2; k++)
+        if (!db->side[k]) CU(cudaStreamCreateWithFlags(&db->side[k], cudaStreamNonBlocking));
+    for (int k = 0; k < 3; k++)
+        if (!db->side_ev[k]) CU(cudaEventCreateWithFlags(&db->side_ev[k], cudaEventDisableTiming));
+    CU(cudaMemsetAsync(d_out, 0, (uint64_t)n * g0.row_bytes, st));
+    CU(cudaEventRecord(db->side_ev[2], st));
+    for (int k = 0; k < 2; k++) CU(cudaStreamWaitEvent(db->side[k], db->side_ev[2], 0));
+    rc = PIR_OK;
+    for (uint32_t i = 0; i < n && rc == PIR_OK; i++)
+        rc = enqueue_answer(db, &qs[i], g0, d_out + (uint64_t)i * g0.row_bytes, db->side[i & 1], /*zero_first=*/false, nullptr,
+                            nullptr, /*throughput=*/n >= 4 && !getenv("PIRB_BATCH_LATENCY_SPLIT"));
+    for (int k = 0; k < 2; k++) {  // join even on failure, so that `st` never runs ahead of the side streams
+        CU(cudaEventRecord(db->side_ev[k], db->side[k]));
+        CU(cudaStreamWaitEvent(st, db->side_ev[k], 0));
+    }
+    return rc;
+}
+
 void compact_answer(const pir_db* db, uint32_t W, const uint8_t* pitched, uint8_t* dense) {
     for (uint32_t c = 0; c < W; c++) memcpy(dense + (size_t)c * db->slot_bytes, pitched + (size_t)c * db->pitch, db->slot_bytes);
 }
@@ -902,11 +934,7 @@ extern "C" int pir_answer_batch_device(pir_db* db, const pir_query* qs, uint32_t
             return fail(PIR_ERR_BAD_ARG, "all queries of a batch must share group_size and is_keyword");
     }
     if (batch_uses_bits_path(db, qs, n_queries, g0)) return enqueue_batch_bits(db, qs, n_queries, g0, (uint8_t*)d_out, st);
-    for (uint32_t i = 0; i < n_queries; i++) {
-        rc = enqueue_answer(db, &qs[i], g0, (uint8_t*)d_out + (uint64_t)i * g0.row_bytes, st);
-        if (rc) return rc;
-    }
-    return PIR_OK;
+    return enqueue_batch_fused(db, qs, n_queries, g0, (uint8_t*)d_out, st);
 }
 
 extern "C" int pir_answer_batch(pir_db* db, const pir_query* qs, uint32_t n_queries, void* out, size_t out_len) {
@@ -931,11 +959,9 @@ extern "C" int pir_answer_batch(pir_db* db, const pir_query* qs, uint32_t n_quer
             return rc;
         }
     } else {
-        for (uint32_t i = 0; i < n_queries; i++) {
-            if ((rc = enqueue_answer(db, &qs[i], g0, db->d_out + (uint64_t)i * g0.row_bytes, db->stream))) {
-                cudaStreamSynchronize(db->stream);
-                return rc;
-            }
+        if ((rc = enqueue_batch_fused(db, qs, n_queries, g0, db->d_out, db->stream))) {
+            cudaStreamSynchronize(db->stream);
+            return rc;
         }
     }
     CU(cudaMemcpyAsync(db->h_out, db->d_out, g0.row_bytes * n_queries, cudaMemcpyDeviceToHost, db->stream));
