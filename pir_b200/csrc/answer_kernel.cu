@@ -30,8 +30,13 @@ extern __shared__ __align__(16) uint8_t g_smem2[];
 
 constexpr int kTreeThreads = 512;
 constexpr int kTreeWarps = kTreeThreads / 32;
-constexpr int kScanWarps = 4;
-constexpr int kAnswerThreads = kTreeThreads + 32 * kScanWarps;
+#ifndef PIRB_SCAN_WARPS
+#define PIRB_SCAN_WARPS 4
+#endif
+constexpr int kScanWarps = PIRB_SCAN_WARPS;
+constexpr int kConsumerWarps = kTreeWarps + kScanWarps;        // warps that may run consume_slices
+constexpr int kAnswerThreads = 32 * kConsumerWarps;            // (the last scan warp also walks the tops of the tasks ahead)
+constexpr uint32_t kHand = 128;                // nodes handed from the top warp to the tree warps per task
 constexpr int kV2MaxDepth = 7;                 // a thread owns at most 2^8 rows (sibling stack: 7 x 16 B)
 constexpr uint32_t kSliceLog = 3;              // rows per thread per slice: at most 8; AnswerPlan::slog_cap picks 4 for shallow tasks
 constexpr uint32_t kRing = 8;                  // slice buffers in flight between tree and scan warps
@@ -46,15 +51,25 @@ constexpr uint32_t kOffPathS = kV2MaxDepth * 4 * kTreeThreads * 4;  // [65] uint
 constexpr uint32_t kOffPathT = kOffPathS + 65 * 16;                 // [65] u8 (+ pad)
 constexpr uint32_t kOffTasks = kOffPathT + 80;                      // task list: header (n, base, stride) + [kMaxTasks] u32
 constexpr uint32_t kTaskHeader = 6;                                 // u32 words before the entries
-constexpr uint32_t kScratchEnd = kOffTasks + 4 * (kTaskHeader + kMaxTasks);
+constexpr uint32_t kOffTopScrS = (kOffTasks + 4 * (kTaskHeader + kMaxTasks) + 15u) & ~15u;  // top warp: [kHand] uint4 level buffer
+constexpr uint32_t kOffTopScrT = kOffTopScrS + kHand * 16;          // [kHand] u8
+constexpr uint32_t kOffPath2S = kOffTopScrT + kHand;                // top warp: [65] uint4 single-node levels
+constexpr uint32_t kOffPath2T = kOffPath2S + 65 * 16;               // [65] u8 (+ pad)
+constexpr uint32_t kOffTopState = kOffPath2T + 80;                  // top walker: next task, Ls of the previous one, its first row
+constexpr uint32_t kScratchEnd = kOffTopState + 16;
 // above the tables (absolute shared-window addresses)
 constexpr uint32_t kAbsLists = kTableEnd;                                      // [20 warps][256] u16
-constexpr uint32_t kAbsRing = kAbsLists + (kAnswerThreads / 32) * kListEntries * 2;  // [kRing][512] u32
+constexpr uint32_t kAbsRing = kAbsLists + kConsumerWarps * kListEntries * 2;    // [kRing][512] u32
 constexpr uint32_t kAbsBars = kAbsRing + kRing * kTreeThreads * 4;             // full[kRing], empty[kRing] u64
 constexpr uint32_t kAbsClaim = kAbsBars + 2 * kRing * 8;                       // claim counter, done[kRing] u32
 constexpr uint32_t kAbsRed = kAbsClaim + 4 * (1 + kRing) + 12;                 // [kMaxRowBytes / 4] u32: the CTA's partial answer
 constexpr uint32_t kMaxRowBytes = 4096;                                        // rows of 16..4096 bytes (power of two)
-constexpr uint32_t kSmemEnd = kAbsRed + kMaxRowBytes;
+constexpr uint32_t kAbsHandS = kAbsRed + kMaxRowBytes;                          // [2][kHand] uint4: top warp -> tree warps
+constexpr uint32_t kAbsHandT = kAbsHandS + 2 * kHand * 16;                     // [2][kHand] u8
+constexpr uint32_t kAbsTopBars = kAbsHandT + 2 * kHand;                        // hand_full[2], hand_empty[2] u64
+constexpr uint32_t kSmemEnd = kAbsTopBars + 4 * 8;
+static_assert(kScratchEnd <= kTableBase, "scratch below the tables overflows into them");
+static_assert(kSmemEnd <= 227u * 1024u, "more shared memory than an sm_100 CTA can have");
 __device__ __forceinline__ uint32_t* red_words() {
     return reinterpret_cast<uint32_t*>(g_smem2 + (kAbsRed - smem_addr(g_smem2)));
 }
@@ -386,12 +401,151 @@ __device__ __forceinline__ void coop_block(const QueryConst& qc, uint32_t k, uin
 }
 
 
+// ---- top role -------------------------------------------------------------------------------------
+// The top of a task (the single-node levels above its node range and the first narrow breadth-first levels)
+// is a chain of dependent AES calls that few threads can work on: executed by the tree warps it costs ~30k
+// cycles per task during which the lookup pipe idles.  With ap.top_warp set, the last scan warp computes it for
+// the tasks ahead while the tree warps are in the depth-first phase of the current one, and hands over the
+// nodes of the deepest level that holds at most kHand of them (level Lh) through a double buffer guarded by
+// mbarriers.  The tree warps still do task 0 themselves (nothing could hide it).  A 21st warp for this would
+// leave 80 registers per thread (a sub-partition holds 16K registers: 6 warps x 32 x 85) and the depth-first
+// loop spills; three scan warps plus a dedicated walker cannot keep up with the row stream (both measured).
+__device__ __forceinline__ uint32_t nodes_at(uint32_t L, uint64_t a, uint32_t m, uint32_t l) {
+    const uint32_t sh = L - l;
+    return (uint32_t)(((a + m - 1u) >> sh) - (a >> sh)) + 1u;
+}
+// level handed over: the deepest level from Ls on with at most kHand nodes (never below the thread roots)
+__device__ __forceinline__ uint32_t hand_level(uint32_t L, uint64_t a, uint32_t m, uint32_t Ls) {
+    uint32_t Lh = Ls;
+    while (Lh < L && nodes_at(L, a, m, Lh + 1u) <= kHand) Lh++;
+    return Lh;
+}
+__device__ __forceinline__ uint32_t hand_full_bar(uint32_t b) { return kAbsTopBars + b * 8u; }
+__device__ __forceinline__ uint32_t hand_empty_bar(uint32_t b) { return kAbsTopBars + (2u + b) * 8u; }
+
+struct TaskTop {  // where a task sits in the tree
+    uint32_t L, m, Ls, Lh;
+    uint64_t a;
+    __device__ __forceinline__ TaskTop(const TaskShape& ts, uint64_t row_start, uint32_t top_bits) {
+        L = top_bits - ts.D;
+        a = row_start >> (ts.D + 1u);
+        m = (a + ts.m_nom <= (1ull << L)) ? ts.m_nom : (uint32_t)((1ull << L) - a);
+        Ls = single_node_levels(L, a, m);
+        Lh = hand_level(L, a, m, Ls);
+    }
+};
+
+__device__ __forceinline__ bool mbar_test(uint32_t addr, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.test_wait.parity.acquire.cta.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n" : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
+    return ok != 0u;
+}
+
+// State of the walker (one warp).  Lane 3*j + k computes PRG block k of the j-th node of a pass (coop_block), so
+// a level of n nodes takes ceil(n / 10) passes of one AES latency each.
+struct TopWalker {
+    // (the state lives in shared memory: it is touched between scan units only, and the scan loop needs its registers)
+    __device__ __forceinline__ static volatile uint32_t* state() { return reinterpret_cast<volatile uint32_t*>(g_smem2 + kOffTopState); }
+    __device__ __forceinline__ static void init() {  // by one thread, before the CTA's first barrier
+        volatile uint32_t* st = state();
+        st[0] = 1u;  // next task to prepare
+        st[1] = 0u;  // Ls of the previous walk
+        st[2] = 0u;  // first row of the previous task (64 bit)
+        st[3] = 0u;
+    }
+    __device__ __forceinline__ static bool pending(uint32_t n_tasks) { return state()[0] < n_tasks; }
+    // Prepare the next task if its hand-over buffer is free; returns false if there was nothing to do (yet).
+    __device__ __forceinline__ static bool try_advance(const QueryConst& qc, uint32_t n_tasks) {
+        volatile uint32_t* stt = state();
+        const uint32_t it = stt[0];
+        if (it >= n_tasks) return false;
+        const uint32_t lane = threadIdx.x & 31u, lc = lane_const();
+        const uint32_t Ls_prev = stt[1];
+        const uint64_t row_prev = ((uint64_t)stt[3] << 32) | stt[2];
+        const uint32_t buf = it & 1u, use = (it - 1u) >> 1;
+        if (use >= 1u) {  // the tree warps must have taken task it-2's nodes
+            uint32_t ok = lane == 0 ? (uint32_t)mbar_test(hand_empty_bar(buf), (use - 1u) & 1u) : 0u;
+            ok = __shfl_sync(0xffffffffu, ok, 0);
+            if (!ok) return false;
+        }
+        const uint32_t top_bits = qc.num_bits - 1u;
+        const uint32_t dyn_base = smem_addr(g_smem2);
+        uint4* path_s = reinterpret_cast<uint4*>(g_smem2 + kOffPath2S);
+        uint8_t* path_t = g_smem2 + kOffPath2T;
+        uint4* scr_s = reinterpret_cast<uint4*>(g_smem2 + kOffTopScrS);
+        uint8_t* scr_t = g_smem2 + kOffTopScrT;
+        uint4* hs = reinterpret_cast<uint4*>(g_smem2 + (kAbsHandS - dyn_base)) + buf * kHand;
+        uint8_t* ht = g_smem2 + (kAbsHandT - dyn_base) + buf * kHand;
+        const TaskIter ti(reinterpret_cast<const uint32_t*>(g_smem2 + kOffTasks));
+        TaskShape ts;
+        uint64_t row_start;
+        ti.decode(it, row_start, ts);
+        const TaskTop tt(ts, row_start, top_bits);
+        const uint32_t k = lane % 3u, jl = lane / 3u;  // block k of the pass's node jl (lanes 30, 31 idle)
+        // single-node levels, restarting below the last node shared with the previous walk
+        uint32_t cp = 0;
+        if (it == 1u) {
+            if (lane == 0) {
+                path_s[0] = make_uint4(qc.s_init[0], qc.s_init[1], qc.s_init[2], qc.s_init[3]);
+                path_t[0] = (uint8_t)qc.t_init;
+            }
+        } else {
+            cp = top_bits + 1u - (64u - (uint32_t)__clzll((long long)(row_start ^ row_prev)));
+            cp = cp < Ls_prev ? cp : Ls_prev;
+            cp = cp < tt.Ls ? cp : tt.Ls;
+        }
+        __syncwarp();
+        // Levels cp .. Ls-1 hold a single node and live in path_s/path_t (one entry per level, kept for the next
+        // restart); from Ls on the levels alternate between the scratch buffer and the hand-over buffer so that
+        // level Lh lands in the latter.  Either way a child is kept if it falls into the next level's node range.
+        for (uint32_t l = cp; l < tt.Lh; l++) {
+            const bool src_hand = ((tt.Lh - l) & 1u) == 0u;
+            const uint4* ss = l <= tt.Ls ? &path_s[l] : (src_hand ? hs : scr_s);
+            const uint8_t* st = l <= tt.Ls ? &path_t[l] : (src_hand ? ht : scr_t);
+            uint4* ds = l < tt.Ls ? &path_s[l + 1] : (src_hand ? scr_s : hs);
+            uint8_t* dt = l < tt.Ls ? &path_t[l + 1] : (src_hand ? scr_t : ht);
+            const uint32_t sh = tt.L - l;
+            const uint64_t lo = tt.a >> sh, lo2 = tt.a >> (sh - 1u);
+            const uint32_t n = nodes_at(tt.L, tt.a, tt.m, l), n2 = nodes_at(tt.L, tt.a, tt.m, l + 1u);
+            const uint32_t skip = (uint32_t)(lo2 - 2ull * lo);  // 1: the first node's left child is out of range
+            for (uint32_t j0 = 0; j0 < n; j0 += 10u) {
+                const uint32_t j = j0 + jl;
+                if (lane < 30u && j < n) {
+                    const uint32_t li = 2u * j - skip, ri = li + 1u;  // (li wraps when the left child is skipped)
+                    const bool lv = (j > 0u || skip == 0u) && li < n2, rv = ri < n2;
+                    coop_block(qc, k, ss[j], st[j], l, lc, lv ? reinterpret_cast<uint8_t*>(&ds[li]) : nullptr, lv ? &dt[li] : nullptr,
+                               rv ? reinterpret_cast<uint8_t*>(&ds[ri]) : nullptr, rv ? &dt[ri] : nullptr);
+                }
+            }
+            __syncwarp();
+        }
+        if (tt.Lh == tt.Ls && lane == 0) {  // (a task whose thread roots hang below a single node)
+            hs[0] = path_s[tt.Ls];
+            ht[0] = path_t[tt.Ls];
+        }
+        if (lane == 0) {
+            mbar_arrive(hand_full_bar(buf));  // (release: the warp's stores are visible to the waiters)
+            stt[1] = tt.Ls;
+            stt[2] = (uint32_t)row_start;
+            stt[3] = (uint32_t)(row_start >> 32);
+            stt[0] = it + 1u;
+        }
+        __syncwarp();
+        return true;
+    }
+};
+
 // ---- consumer loop (scan warps all along, tree warps once they have nothing left to expand) ----------
 // Work unit = one 32-word group of one slice, claimed in order from a shared counter, so the backlog at
 // the end of the kernel is drained by all 20 warps.  The warp that completes a slice's last group hands
 // the ring slot back to the tree warps.
 template <int NCB>
-__device__ __forceinline__ void consume_slices(const AnswerPlan& ap, uint32_t warp_in_cta) {
+__device__ __forceinline__ void consume_slices(const QueryConst& qc, const AnswerPlan& ap, uint32_t warp_in_cta, const bool DUAL) {
     const uint32_t lane = threadIdx.x & 31u;
     const ScanLane sl = scan_lane(ap);
     const uint32_t dyn_base = smem_addr(g_smem2);
@@ -406,6 +560,8 @@ __device__ __forceinline__ void consume_slices(const AnswerPlan& ap, uint32_t wa
     for (int cb = 0; cb < NCB; cb++) acc[cb] = make_uint4(0, 0, 0, 0);
     long long c_wait = 0;
     const long long c_in = ap.dbg ? clock64() : 0;
+    // DUAL: this scan warp also walks the tops of the tasks ahead (TopWalker), before anything else whenever a
+    // hand-over buffer is free -- the tree warps will wait for it at the next task boundary, the scan has slack.
     while (true) {
         uint32_t u = 0;
         if (lane == 0) u = atomicAdd(claim, 1u);
@@ -423,6 +579,16 @@ __device__ __forceinline__ void consume_slices(const AnswerPlan& ap, uint32_t wa
         if (!have) break;
         const uint32_t slot = gsl & (kRing - 1u), par = (gsl / kRing) & 1u;
         const long long cw0 = (ap.dbg && warp_in_cta == kTreeWarps) ? clock64() : 0;
+        if (DUAL) {
+            // This warp also walks the tops of the tasks ahead, before anything else whenever a hand-over buffer is
+            // free: the tree warps will wait for it at the next task boundary, the scan has slack.  The slice just
+            // claimed may belong to a task whose top is still to be walked, so never block on it while tops are pending.
+            while (TopWalker::pending(ti.n)) {
+                if (TopWalker::try_advance(qc, ti.n)) continue;
+                uint32_t ok = lane == 0 ? (uint32_t)mbar_test(full_bar(slot), par) : 0u;
+                if (__shfl_sync(0xffffffffu, ok, 0)) break;
+            }
+        }
         mbar_wait(full_bar(slot), par);
         if (ap.dbg && warp_in_cta == kTreeWarps) c_wait += clock64() - cw0;
         uint64_t grow0;
@@ -444,6 +610,7 @@ __device__ __forceinline__ void consume_slices(const AnswerPlan& ap, uint32_t wa
             }
         }
     }
+    // (DUAL: no top can be pending here -- units run out only once the tree warps are in the CTA's last task)
     if (ap.dbg && warp_in_cta == kTreeWarps && lane == 0) {  // first scan warp: cycles scanning vs waiting for slices
         ap.dbg[11264ull + blockIdx.x] = ((unsigned long long)(clock64() - c_in - c_wait) << 32) | (unsigned long long)(c_wait & 0xffffffffll);
     }
@@ -497,7 +664,22 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
         //    They are kept in path_s/path_t, and the walk restarts below the last node shared with the
         //    previous task. --
         const uint32_t Ls = single_node_levels(L, a, m);
-        {
+        uint32_t l_bfs = Ls;  // first breadth-first level the tree warps expand themselves
+        if (ap.top_warp && it > 0u) {
+            // the top warp has walked this task's top while we were in the previous task's depth-first phase
+            const uint32_t Lh = hand_level(L, a, m, Ls);
+            const uint32_t buf = it & 1u, use = (it - 1u) >> 1;
+            const uint32_t dyn_base = smem_addr(g_smem2);
+            mbar_wait(hand_full_bar(buf), use & 1u);
+            bar_sync(BAR_TREE, kTreeThreads);  // (the BFS buffers alias the sibling stacks of warps still in the previous task)
+            if (tid < nodes_at(L, a, m, Lh)) {
+                bfs_s[(Lh & 1u) * kTreeThreads + tid] = reinterpret_cast<const uint4*>(g_smem2 + (kAbsHandS - dyn_base))[buf * kHand + tid];
+                bfs_t[(Lh & 1u) * kTreeThreads + tid] = (g_smem2 + (kAbsHandT - dyn_base))[buf * kHand + tid];
+            }
+            bar_sync(BAR_TREE, kTreeThreads);
+            if (tid == 0) mbar_arrive(hand_empty_bar(buf));
+            l_bfs = Lh;
+        } else {
             uint32_t cp = 0;
             if (it == 0) {
                 if (tid == 0) {
@@ -532,11 +714,11 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
                 bfs_s[(Ls & 1u) * kTreeThreads] = path_s[Ls];
                 bfs_t[(Ls & 1u) * kTreeThreads] = path_t[Ls];
             }
+            bar_sync(BAR_TREE, kTreeThreads);
         }
-        bar_sync(BAR_TREE, kTreeThreads);
         // -- part 2: breadth-first over the node range, level by level.  Level l holds nodes
         //    [a >> (L-l), (a+m-1) >> (L-l)]; a child is kept if it falls into the next level's range. --
-        for (uint32_t l = Ls; l < L; l++) {
+        for (uint32_t l = l_bfs; l < L; l++) {
             const uint32_t sh = L - l;
             const uint64_t lo = a >> sh, lo2 = a >> (sh - 1u);
             const uint32_t n = (uint32_t)(((a + m - 1u) >> sh) - lo) + 1u;
@@ -697,7 +879,7 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
         atomicMax(ap.dbg + 10240ull + blockIdx.x, (unsigned long long)(total_u > claimed ? total_u - claimed : 0u) + 1ull);
     }
     // nothing left to expand: help the scan warps drain the ring
-    if constexpr (NCB != 0) consume_slices<NCB>(ap, warp);
+    if constexpr (NCB != 0) consume_slices<NCB>(qc, ap, warp, false);
     PHASE(c_tail)
 #undef PHASE
     if (ap.dbg && tid == 0) {
@@ -735,6 +917,8 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
             mbar_init(full_bar(k), kTreeWarps);
             mbar_init(empty_bar(k), 1);
         }
+        for (uint32_t k = 0; k < 4; k++) mbar_init(kAbsTopBars + k * 8u, 1);  // hand_full[2], hand_empty[2]
+        TopWalker::init();
         uint32_t* claim = reinterpret_cast<uint32_t*>(g_smem2 + (kAbsClaim - base));
         for (uint32_t k = 0; k < 1 + kRing; k++) claim[k] = 0;
     }
@@ -742,7 +926,14 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
     if (threadIdx.x < kTreeThreads) {
         tree_role<NCB, FCW_ODD>(qc, ap, lane_const(), c_entry);
     } else {
-        if constexpr (NCB != 0) consume_slices<NCB>(ap, threadIdx.x >> 5);
+        // the last scan warp doubles as the top walker
+        const bool dual = ap.top_warp != 0u && threadIdx.x >= kAnswerThreads - 32;
+        if constexpr (NCB != 0) {
+            consume_slices<NCB>(qc, ap, threadIdx.x >> 5, dual);
+        } else if (dual) {
+            const uint32_t n_tasks = *reinterpret_cast<const uint32_t*>(g_smem2 + kOffTasks);
+            while (TopWalker::pending(n_tasks)) TopWalker::try_advance(qc, n_tasks);
+        }
     }
     if constexpr (NCB != 0) {  // (BITS mode has nothing to fold)
         __syncthreads();

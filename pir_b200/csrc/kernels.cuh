@@ -43,7 +43,8 @@ struct AnswerPlan {
     uint32_t Dmin;        // binary (hi_warps == 0): chunks of 2^(10+Dmin) rows covered by aligned tasks of depth Dmin..D
     uint32_t pad;         // debug flags
     uint32_t slog_cap;    // log2(rows per thread per slice) at most: 3, or 2 when tasks are so shallow that the last
-    uint32_t pad2;        //   slice (whose rows are scanned after the tree warps are done) would be a large part of a CTA's work
+    uint32_t top_warp;    //   slice (whose rows are scanned after the tree warps are done) would be a large part of a CTA's work
+                          // top_warp != 0: an extra warp walks the top of task k+1 during the depth-first phase of task k
     uint32_t* out;        // row_bytes/4 words, XOR-accumulated (atomics); the caller zeroes
     uint32_t* bits_out;   // BITS mode (non-null): packed selection bits, bit i = row first_row + i, OR-accumulated
                           // into a zeroed buffer of ceil(n_rows/32)+1 words; no rows are read
