@@ -1,7 +1,7 @@
 // aes_unrolled.cuh — the hot-loop form of the PRG node expansion (dpf/common.go:62-75 +
-// dpf/server.go:68-92): all AES rounds unrolled so that every round-key word is a constant-bank
-// operand of the LOP3 that consumes it (no LDC, no register moves), and only the table lookups whose
-// output bytes are actually used downstream are issued:
+// dpf/server.go:68-92): AES rounds unrolled (kRoundUnroll* below) so that round-key words are constant-bank
+// operands of the LOP3 that consumes them, and only the table lookups whose output bytes are actually used
+// downstream are issued:
 //
 //   block 0 (sL):            rounds 1-9 full, last round 16 lookups (8 at a leaf parent)
 //   block 1 (tL, sR[0:15]):  rounds 1-9 full, last round 16 lookups (9 at a leaf parent)
@@ -14,6 +14,21 @@
 
 namespace pirb {
 
+// How far the middle rounds are unrolled.  Fully unrolled, every round-key word is a constant-bank operand
+// (LDCU into a uniform register) but the depth-first loop is ~27 KB of code; the four tree warps of a
+// sub-partition sit at different places in it and stall on instruction fetch when it does not fit.  Odd-FinalCW
+// keys (lookup pipe 92 % busy, no_instruction 0.08 per issue) keep the full unroll.  The even-FinalCW loop, with
+// block 2 under a condition, measured no_instruction 0.20 per issue: three iterations of three rounds (round keys
+// then come through per-thread LDC.64) are 1.6 % faster on 2^24 x 256 B and 3-5 % on the shards of 2-8 GPUs
+// (profiles/r1_round_unroll.txt).
+#ifndef PIRB_ROUND_UNROLL_ODD
+#define PIRB_ROUND_UNROLL_ODD 8
+#endif
+#ifndef PIRB_ROUND_UNROLL_EVEN
+#define PIRB_ROUND_UNROLL_EVEN 3
+#endif
+constexpr int kRoundUnrollOdd = PIRB_ROUND_UNROLL_ODD, kRoundUnrollEven = PIRB_ROUND_UNROLL_EVEN;
+
 // state after round 9 for blocks 0,1 and after round 8 for block 2
 __device__ __forceinline__ void aes3_main_rounds(const QueryConst& qc, const uint32_t s[4], uint32_t lc,
                                                  uint32_t a[3][4]) {
@@ -21,7 +36,7 @@ __device__ __forceinline__ void aes3_main_rounds(const QueryConst& qc, const uin
     for (int k = 0; k < 3; k++)
 #pragma unroll
         for (int c = 0; c < 4; c++) a[k][c] = s[c] ^ qc.rk[k][c];
-#pragma unroll
+#pragma unroll kRoundUnrollOdd
     for (int r = 1; r <= 8; r++) {
         uint32_t n[3][4];
 #pragma unroll
@@ -125,7 +140,7 @@ __device__ __forceinline__ void aes3_main_rounds_cond(const QueryConst& qc, cons
 #pragma unroll
         for (int c = 0; c < 4; c++) a[2][c] = s[c] ^ qc.rk[2][c];
     }
-#pragma unroll
+#pragma unroll kRoundUnrollEven
     for (int r = 1; r <= 9; r++) {
         uint32_t n[3][4];
 #pragma unroll
