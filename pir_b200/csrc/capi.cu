@@ -346,7 +346,7 @@ struct AnswerSplit {
 double uniform_task_cost(uint32_t top_bits, uint32_t D, uint32_t hiw) {
     const double top = 1300.0 * (double)(top_bits - D) + 12000.0 + (hiw < 16u ? 2500.0 : 0.0);
     const double n_hi = (double)((2u << D) - 1u), n_lo = hiw < 16u ? (double)((1u << D) - 1u) : n_hi;
-    const double pen = hiw >= 16u ? 1.0 : hiw == 12u ? 1.12 : hiw == 8u ? 1.25 : 1.7;
+    const double pen = hiw >= 16u ? 1.0 : hiw == 12u ? 1.08 : hiw == 8u ? 1.25 : 1.7;
     return top + 1718.0 * (4.0 * n_lo + (double)(hiw / 4u) * (n_hi - n_lo) * pen);
 }
 // throughput: many independent launches run back to back on two streams (batches), so a CTA that finishes
