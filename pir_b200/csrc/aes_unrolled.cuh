@@ -16,13 +16,15 @@ namespace pirb {
 
 // How far the middle rounds are unrolled.  Fully unrolled, every round-key word is a constant-bank operand
 // (LDCU into a uniform register) but the depth-first loop is ~27 KB of code; the four tree warps of a
-// sub-partition sit at different places in it and stall on instruction fetch when it does not fit.  Odd-FinalCW
-// keys (lookup pipe 92 % busy, no_instruction 0.08 per issue) keep the full unroll.  The even-FinalCW loop, with
-// block 2 under a condition, measured no_instruction 0.20 per issue: three iterations of three rounds (round keys
-// then come through per-thread LDC.64) are 1.6 % faster on 2^24 x 256 B and 3-5 % on the shards of 2-8 GPUs
-// (profiles/r1_round_unroll.txt).
+// sub-partition sit at different places in it and stall on instruction fetch when it does not fit (the
+// even-FinalCW loop, with block 2 under a condition, measured no_instruction 0.20 per issue).  Partly rolled,
+// round keys come through per-thread LDC.64 instead.  Measured on 2^24 x 256 B and its shards
+// (profiles/r1_round_unroll.txt): even-FinalCW keys are fastest with three iterations of three rounds (1.6 % on
+// the whole database, 3-5 % on the shards of 2-8 GPUs); odd-FinalCW keys (lookup pipe 92 % busy) with two
+// iterations of four (0.4 % and 2 %) now that every shard runs one task per CTA whose lo warps leave the loop
+// early -- with sixteen warps in the loop all the time the full unroll was ahead.
 #ifndef PIRB_ROUND_UNROLL_ODD
-#define PIRB_ROUND_UNROLL_ODD 8
+#define PIRB_ROUND_UNROLL_ODD 4
 #endif
 #ifndef PIRB_ROUND_UNROLL_EVEN
 #define PIRB_ROUND_UNROLL_EVEN 3

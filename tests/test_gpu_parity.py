@@ -235,6 +235,25 @@ def test_batch_two_phase_path_matches_oracle(gpu_lib, monkeypatch, db_size, slot
             assert np.array_equal(got[i], oracle.answer(o, data, db_size, slot_bytes)), i
 
 
+@pytest.mark.parametrize("db_size,slot_bytes,W,nq", [(3000, 100, 3, 4), (5000, 512, 1, 5), (1 << 15, 256, 1, 6)])
+def test_batch_paths_are_repeatable(gpu_lib, monkeypatch, db_size, slot_bytes, W, nq):
+    """The batch paths run kernels on two side streams against per-handle scratch: the same batch, answered 40
+    times by fresh handles through both paths, must give the oracle's bytes every time (a race would not)."""
+    data = oracle.synth_fill(21, 0, db_size, slot_bytes)
+    rows = db_size // W
+    rng = np.random.default_rng(nq)
+    pairs = [make_queries(100 + i, db_size, W, int(idx)) for i, idx in enumerate(rng.integers(0, rows, size=nq))]
+    qs = [p[1][i & 1] for i, p in enumerate(pairs)]
+    want = np.stack([np.asarray(oracle.answer(p[0][i & 1], data, db_size, slot_bytes)).reshape(-1) for i, p in enumerate(pairs)])
+    for rep in range(40):
+        with Handle(db_size, slot_bytes) as h:
+            h.fill(21)
+            for mode in ("bits", "fused"):
+                monkeypatch.setenv("PIRB_BATCH_MODE", mode)
+                got = np.asarray(h.answer_batch(qs)).reshape(nq, -1)
+                assert np.array_equal(got, want), (rep, mode)
+
+
 @pytest.mark.parametrize("kind", ["dense_sorted", "duplicates", "unsorted", "clustered", "wide64"])
 def test_keyword_prefix_sharing_kernel_matches_oracle(gpu_lib, monkeypatch, kind):
     """The keyword path restarts each row's walk below the last node it shares with the previous row
