@@ -3,7 +3,7 @@ timeout 900 ncu --set full --clock-control none --import-source on -k regex:answ
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:answer_kernel --launch-skip 12 -c 1 -o gpurun_out/answer_${V}_odd -f python tools/parity_probe.py > gpurun_out/ncu_full_${V}_odd.log 2>&1; echo rc=$?
 # of the answer kernel, and the in-kernel phase counters.  V names the output generation.
 set -x
-V=${V:-v12}
+V=${V:-v13}
 timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/gpu_tests_${V}.log 2>&1; tail -3 gpurun_out/gpu_tests_${V}.log
 python bench.py > gpurun_out/bench_${V}_default.json 2> gpurun_out/bench_${V}_default.err; echo rc=$?
 python bench.py --steps 40 --warmup 5 > gpurun_out/bench_${V}.json 2> gpurun_out/bench_${V}.err; echo rc=$?

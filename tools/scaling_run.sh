@@ -1,7 +1,7 @@
 #!/bin/bash
 # bench.py at N = 1, 2, 4, 8 on one 8-GPU box, plus the multi-GPU tests (run under gpurun --gpus 8)
 set -x
-V=${V:-v12}
+V=${V:-v13}
 timeout 600 python -m pytest tests -m gpu -x -q > gpurun_out/tests_${V}_8gpu.log 2>&1; tail -3 gpurun_out/tests_${V}_8gpu.log
 python bench.py --steps 40 --warmup 5 > gpurun_out/bench_${V}_n1.json 2> gpurun_out/bench_${V}_n1.err
 for N in 2 4 8; do
