@@ -16,7 +16,8 @@
 //                through shared memory (TMA / cp.async) would cost more than it hides.
 // Hand-off is a producer/consumer ring of kRing slice buffers guarded by mbarriers (full: 16 tree warps
 // arrive, empty: the scan warps arrive).  The answer is reduced per CTA and XORed into global memory
-// (possibly a peer GPU's) with one atomic per word.
+// (possibly a peer GPU's) with one atomic per word.  When a CTA has several tasks, the last scan warp also
+// walks the narrow top of the tasks ahead (TopWalker) so that the tree warps find it ready.
 //
 // Why deep tasks: the top of a task is executed by few warps and is bound by single-warp issue latency
 // (~1.7k cycles per level, measured), during which the lookup pipe idles.  A thread that owns 2^(d+1)
