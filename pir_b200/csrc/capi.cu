@@ -793,7 +793,10 @@ void fill_answer_split(pir_db* db, const QueryGeom& g, AnswerPlan* ap, bool thro
     // Slices of 8 rows per thread, or of 4 when the task a CTA ends with is shallow: the rows of the last slice
     // are scanned after the tree warps are done, and with 32 rows per thread that slice is a quarter of the task.
     ap->slog_cap = (ap->hi_warps != 0u && ap->D <= 4u) ? 2u : 3u;
-    ap->top_warp = 1u;  // the next task's top is walked by an extra warp during the current task's depth-first phase
+    // The last scan warp walks the tops of the tasks ahead (answer_kernel.cu TopWalker).  It pays when the scan warps
+    // have slack: 2^24 x 256 B in several tasks per CTA 0.943 -> 0.937 ms; with 32-byte rows they have none
+    // (2^28 x 32 B: 13.05 ms without the walker, 13.22 ms with it).
+    ap->top_warp = g.row_bytes >= 128u ? 1u : 0u;
     if (const char* e = getenv("PIRB_TOP_WARP")) ap->top_warp = atoi(e) ? 1u : 0u;  // development aid (A/B)
     if (const char* e = getenv("PIRB_SLICE_LOG")) {  // development aid
         const uint32_t f = (uint32_t)atoi(e);
