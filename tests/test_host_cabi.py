@@ -159,3 +159,29 @@ def test_multi_gpu_entry_points_fail_loudly_without_device():
     assert L.pir_combine_create(0, 0, 256, C.byref(h)) == _capi.PIR_ERR_BAD_ARG
     assert L.pir_combine_create(0, 4, 100, C.byref(h)) == _capi.PIR_ERR_BAD_ARG
     assert L.pir_server_create(devs, 0, 1024, 32, 1, C.byref(h)) == _capi.PIR_ERR_BAD_ARG
+
+
+def test_work_split_chooser_is_valid_for_typical_shards():
+    """choose_answer_split (capi.cu) for the shards of the BASELINE configs: the split it returns is one the answer
+    kernel accepts (launch_answer's checks), and the headline database gets one task per CTA at every shard size."""
+    L = _capi.lib()
+    f = L.pir_debug_answer_split
+    f.argtypes = [C.c_uint32, C.c_uint64, C.c_uint64, C.c_int] + [C.POINTER(C.c_uint32)] * 3
+    f.restype = None
+    sms = 148
+    for logn in (10, 16, 20, 22, 24, 26, 28):
+        for frac in (1, 2, 4, 8):
+            n = (1 << logn) // frac
+            d, dmin, hiw = C.c_uint32(), C.c_uint32(), C.c_uint32()
+            f(logn + 1, (frac - 1) * n, n, sms, C.byref(d), C.byref(dmin), C.byref(hiw))
+            assert d.value <= 7 and d.value + 1 <= logn + 1
+            assert hiw.value in (0, 4, 8, 12, 16)
+            if hiw.value == 0:
+                assert dmin.value <= d.value
+            else:
+                assert hiw.value == 16 or d.value > 0
+                if logn == 24:  # one uniform task per CTA: R = 2^(D+5) * (16 + hi_warps) rows cover the shard in <= 148 tasks
+                    rows_per_task = (16 + hiw.value) << (d.value + 5)
+                    assert (n + rows_per_task - 1) // rows_per_task <= sms
+            if logn == 24:
+                assert hiw.value == 12 and d.value == 7 - (frac.bit_length() - 1)
