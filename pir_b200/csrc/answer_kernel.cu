@@ -57,7 +57,8 @@ constexpr uint32_t kOffTopScrT = kOffTopScrS + kHand * 16;          // [kHand] u
 constexpr uint32_t kOffPath2S = kOffTopScrT + kHand;                // top warp: [65] uint4 single-node levels
 constexpr uint32_t kOffPath2T = kOffPath2S + 65 * 16;               // [65] u8 (+ pad)
 constexpr uint32_t kOffTopState = kOffPath2T + 80;                  // top walker: next task, Ls of the previous one, its first row
-constexpr uint32_t kScratchEnd = kOffTopState + 16;
+constexpr uint32_t kOffRk = kOffTopState + 16;                      // [3][44] u32: the round keys, for quad_path_walk
+constexpr uint32_t kScratchEnd = kOffRk + 3 * 44 * 4;
 // above the tables (absolute shared-window addresses)
 constexpr uint32_t kAbsLists = kTableEnd;                                      // [20 warps][256] u16
 constexpr uint32_t kAbsRing = kAbsLists + kConsumerWarps * kListEntries * 2;    // [kRing][512] u32
@@ -402,6 +403,64 @@ __device__ __forceinline__ void coop_block(const QueryConst& qc, uint32_t k, uin
 }
 
 
+// ---- the single-node levels, by twelve lanes of one warp -------------------------------------------------
+// The levels above a task that hold a single node are one chain of dependent AES calls: what counts is latency.
+// Lane 4*k + c (k = 0..2, c = 0..3) computes column c of PRG block k: 3 SHFL (the other columns of the previous
+// round) + 4 PRMT + 4 LDS + 2 LOP3 per round, 86 cycles against 135 for a thread that computes a whole block
+// (profiles/r1_latency_probe.txt).  The node stays in registers from level to level (the chosen child's words
+// come back by SHFL), because handing it over through shared memory costs ~600 cycles per level, as much as six
+// rounds; every level is also stored to path_s/path_t, off the critical path, for the restart of later tasks.
+// Round keys come from shared memory (conflict-free: the twelve words of a round lie in twelve banks).
+// Levels [l0, l1) of the walk towards node `a` of level L; path_s[l0], path_t[l0] hold the start node.
+__device__ __forceinline__ void quad_path_walk(const QueryConst& qc, uint32_t lc, uint64_t a, uint32_t L, uint32_t l0, uint32_t l1,
+                                               uint4* path_s, uint8_t* path_t, unsigned long long* dbg = nullptr) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t c = lane & 3u, k = (lane >> 2) % 3u, g0 = lane & ~3u;  // (lanes 12..31 run along and store nothing)
+    const uint32_t* rk = reinterpret_cast<const uint32_t*>(g_smem2 + kOffRk) + k * 44u + c;
+    uint32_t sw = reinterpret_cast<const uint32_t*>(&path_s[l0])[c];
+    uint32_t t = path_t[l0];
+    for (uint32_t l = l0; l < l1; l++) {
+        const uint32_t cwc = qc.cw[l][c] & (0u - t);
+        const uint32_t bit = (uint32_t)(a >> (L - 1u - l)) & 1u;
+        uint32_t x = sw ^ rk[0];
+        uint32_t x1, x2, x3;
+#pragma unroll 1
+        for (int r = 1; r <= 9; r++) {
+            x1 = __shfl_sync(0xffffffffu, x, g0 + ((c + 1u) & 3u));
+            x2 = __shfl_sync(0xffffffffu, x, g0 + ((c + 2u) & 3u));
+            x3 = __shfl_sync(0xffffffffu, x, g0 + ((c + 3u) & 3u));
+            const uint32_t v0 = lds0(__byte_perm(x, lc, 0x7604));
+            const uint32_t v1 = lds0(__byte_perm(x1, lc, 0x7615));
+            const uint32_t v2 = lds1(__byte_perm(x2, lc, 0x7624));
+            const uint32_t v3 = lds1(__byte_perm(x3, lc, 0x7635));
+            x = v0 ^ v1 ^ v2 ^ v3 ^ rk[4 * r];
+        }
+        x1 = __shfl_sync(0xffffffffu, x, g0 + ((c + 1u) & 3u));
+        x2 = __shfl_sync(0xffffffffu, x, g0 + ((c + 2u) & 3u));
+        x3 = __shfl_sync(0xffffffffu, x, g0 + ((c + 3u) & 3u));
+        uint32_t o;
+        {
+            const uint32_t v0 = lds1(__byte_perm(x, lc, 0x7604));   // T2[.]: S in byte 0
+            const uint32_t v1 = lds1(__byte_perm(x1, lc, 0x7615));  // T3[.]: S in byte 1
+            const uint32_t v2 = lds0(__byte_perm(x2, lc, 0x7624));  // T0[.]: S in byte 2
+            const uint32_t v3 = lds0(__byte_perm(x3, lc, 0x7635));  // T1[.]: S in byte 3
+            const uint32_t lo = __byte_perm(v0, v1, 0x7650), hi = __byte_perm(v2, v3, 0x7210);
+            o = __byte_perm(lo, hi, 0x7610) ^ rk[40] ^ sw;          // (Matyas-Meyer-Oseas feed-forward)
+        }
+        const uint32_t nxt = __shfl_down_sync(0xffffffffu, o, 1);   // block 1: the next PRG output word (block 2's word 0 after word 3)
+        // lanes 0..3: the left child's seed words; lanes 4..7: the right child's; lane 4: tL, lane 8: tR
+        const uint32_t child = (k == 0u ? o : __funnelshift_r(o, nxt, 8)) ^ cwc;
+        const uint32_t tbit = k == 1u ? ((o & 1u) ^ (t & (uint32_t)(qc.cw_tl >> l) & 1u))
+                                      : (((o >> 8) & 1u) ^ (t & (uint32_t)(qc.cw_tr >> l) & 1u));
+        sw = __shfl_sync(0xffffffffu, child, (bit ? 4u : 0u) + c);
+        t = __shfl_sync(0xffffffffu, tbit, bit ? 8u : 4u);
+        if (lane < 4u) reinterpret_cast<uint32_t*>(&path_s[l + 1])[c] = sw;
+        if (lane == 0) path_t[l + 1] = (uint8_t)t;
+        if (dbg && lane == 0) dbg[14336ull + l] = (unsigned long long)clock64();
+    }
+    __syncwarp();
+}
+
 // ---- top role -------------------------------------------------------------------------------------
 // The top of a task (the single-node levels above its node range and the first narrow breadth-first levels)
 // is a chain of dependent AES calls that few threads can work on: executed by the tree warps it costs ~30k
@@ -702,18 +761,12 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
                 cp = cp < Ls_prev ? cp : Ls_prev;
                 cp = cp < Ls ? cp : Ls;
             }
-            for (uint32_t l = cp; l < Ls; l++) {
-                if (coop_warp && cj == 0) {
-                    const uint32_t bit = (uint32_t)(a >> (L - 1u - l)) & 1u;
-                    uint8_t* ds = reinterpret_cast<uint8_t*>(&path_s[l + 1]);
-                    coop_block(qc, ck, path_s[l], path_t[l], l, lc, bit ? nullptr : ds, bit ? nullptr : &path_t[l + 1],
-                               bit ? ds : nullptr, bit ? &path_t[l + 1] : nullptr);
+            if (warp == 0u) {  // one warp walks the whole chain, the node stays in registers (no CTA barrier per level)
+                quad_path_walk(qc, lc, a, L, cp, Ls, path_s, path_t, (ap.dbg && blockIdx.x == 0 && it == 0) ? ap.dbg : nullptr);
+                if (lane == 0) {
+                    bfs_s[(Ls & 1u) * kTreeThreads] = path_s[Ls];
+                    bfs_t[(Ls & 1u) * kTreeThreads] = path_t[Ls];
                 }
-                bar_sync(BAR_TREE, kTreeThreads);
-            }
-            if (tid == 0) {
-                bfs_s[(Ls & 1u) * kTreeThreads] = path_s[Ls];
-                bfs_t[(Ls & 1u) * kTreeThreads] = path_t[Ls];
             }
             bar_sync(BAR_TREE, kTreeThreads);
         }
@@ -912,6 +965,7 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
     const uint32_t words_out = (uint32_t)(ap.row_bytes >> 2);
     if constexpr (NCB != 0)
         for (uint32_t i = threadIdx.x; i < words_out; i += kAnswerThreads) red[i] = 0;
+    if (threadIdx.x < 3 * 44) reinterpret_cast<uint32_t*>(g_smem2 + kOffRk)[threadIdx.x] = qc.rk[threadIdx.x / 44][threadIdx.x % 44];
     if (threadIdx.x == kAnswerThreads - 1) build_task_list(ap, reinterpret_cast<uint32_t*>(g_smem2 + kOffTasks));
     if (threadIdx.x == kAnswerThreads - 2) {
         for (uint32_t k = 0; k < kRing; k++) {

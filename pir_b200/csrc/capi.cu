@@ -655,8 +655,8 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
         static const bool phase_debug = getenv("PIRB_PHASE_DEBUG") != nullptr;
         unsigned long long* d_dbg = nullptr;
         if (phase_debug) {
-            CU(cudaMalloc(&d_dbg, 8 * 14 * 1024));
-            CU(cudaMemsetAsync(d_dbg, 0, 8 * 14 * 1024, st));
+            CU(cudaMalloc(&d_dbg, 8 * 15 * 1024));
+            CU(cudaMemsetAsync(d_dbg, 0, 8 * 15 * 1024, st));
             ap.dbg = d_dbg;
         }
         cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -674,9 +674,9 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
         CU(launch_answer(qc, ap, ctx.d_t0, ctx.smem_base, ctx.num_sms, st));
         if (e1) CU(cudaEventRecord(e1, st));
         if (d_dbg) {  // development aid: average per-CTA cycles per phase of the tree warps, to stderr
-            std::vector<unsigned long long> h(14 * 1024);
+            std::vector<unsigned long long> h(15 * 1024);
             CU(cudaStreamSynchronize(st));
-            CU(cudaMemcpy(h.data(), d_dbg, 8 * 14 * 1024, cudaMemcpyDeviceToHost));
+            CU(cudaMemcpy(h.data(), d_dbg, 8 * 15 * 1024, cudaMemcpyDeviceToHost));
             cudaFree(d_dbg);
             double sum[8] = {0}, mx = 0;
             int n = 0;
@@ -694,6 +694,9 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
                     if (h[13312 + b] > g1) g1 = h[13312 + b];
                     if (h[13312 + b] < ge_first) ge_first = h[13312 + b];
                 }
+            if (getenv("PIRB_PHASE_DEBUG")[0] == '3')
+                for (int l = 1; l < 64; l++)
+                    if (h[14336 + l] && h[14336 + l - 1]) fprintf(stderr, "[top cta0] level %d took %llu cycles\n", l, h[14336 + l] - h[14336 + l - 1]);
             if (n) fprintf(stderr, "[phase] globaltimer: first CTA start to last CTA start %llu ns, first CTA end at %llu ns, last CTA end at %llu ns\n",
                            gs_last - g0, ge_first - g0, g1 - g0);
             if (getenv("PIRB_PHASE_DEBUG")[0] == '2')
