@@ -996,7 +996,25 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
             const uint32_t v = red[i];
             if (v) atomicXor(&ap.out[i], v);
         }
-        if (ap.arrivals) {
+        if (ap.host_out) {
+            // Host call on one GPU: every CTA's XORs are fenced and counted; the last CTA reads the finished words
+            // (atomicExch: the read also re-zeroes the accumulator for the next query) and stores them to the
+            // caller's mapped pinned buffer, visible to the host once the kernel has completed.
+            __threadfence();
+            __syncthreads();
+            uint32_t* flag = reinterpret_cast<uint32_t*>(g_smem2 + (kAbsClaim - smem_addr(g_smem2)));  // (free by now)
+            if (threadIdx.x == 0) {
+                const bool last = atomicAdd(ap.cta_done, 1u) == gridDim.x - 1u;
+                if (last) *ap.cta_done = 0u;  // ready for the launch that reuses this counter
+                *flag = last ? 1u : 0u;
+            }
+            __syncthreads();
+            if (*flag) {
+                __threadfence();
+                for (uint32_t i = threadIdx.x; i < words_out; i += kAnswerThreads) ap.host_out[i] = atomicExch(&ap.out[i], 0u);
+                __threadfence_system();
+            }
+        } else if (ap.arrivals) {
             // Multi-GPU combine: this shard's partial is complete once every CTA's XORs are visible.  Each thread
             // fences its own atomics (the slot may live on a peer GPU), the CTA counts itself in, and the last
             // CTA of the launch publishes the arrival (kernels.cu wait_arrivals_kernel acquires it on the owner).

@@ -217,6 +217,8 @@ struct pir_db {
     uint8_t* d_out = nullptr;
     uint64_t out_cap = 0;
     uint8_t* h_out = nullptr;  // pinned
+    uint32_t* h_out_dev = nullptr;  // the same buffer as the device sees it (cudaHostGetDevicePointer)
+    bool out_zeroed = false;        // d_out holds zeros: the answer kernel's last CTA left it so (AnswerPlan::host_out)
     uint64_t h_out_cap = 0;
     // cached work split of the answer kernel for the last (num_bits, shard rows) seen
     uint32_t split_nb = 0, split_d = 0, split_hiw = 0, split_dmin = 0;
@@ -272,13 +274,18 @@ int ensure_out(pir_db* db, uint64_t n) {
         db->out_cap = 0;
         CU(cudaMalloc(&db->d_out, n));
         db->out_cap = n;
+        db->out_zeroed = false;
     }
     if (n > db->h_out_cap) {
         if (db->h_out) cudaFreeHost(db->h_out);
         db->h_out = nullptr;
         db->h_out_cap = 0;
+        db->h_out_dev = nullptr;
         CU(cudaMallocHost(&db->h_out, n));
         db->h_out_cap = n;
+        void* dp = nullptr;
+        if (cudaHostGetDevicePointer(&dp, db->h_out, 0) == cudaSuccess) db->h_out_dev = (uint32_t*)dp;
+        else cudaGetLastError();  // (no mapped access: the host calls keep the memset + copy path)
     }
     return PIR_OK;
 }
@@ -611,7 +618,8 @@ constexpr uint32_t kCtaDoneRing = 64;
 // bumps *arrivals itself (system scope, after its partial has been XORed into d_out) and *signalled is set;
 // on every other path the caller launches the signalling kernel.
 int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* d_out, cudaStream_t st,
-                   bool zero_first = true, uint32_t* arrivals = nullptr, bool* signalled = nullptr, bool throughput = false) {
+                   bool zero_first = true, uint32_t* arrivals = nullptr, bool* signalled = nullptr, bool throughput = false,
+                   uint32_t* host_out = nullptr) {
     // every kernel below XOR-accumulates into d_out (atomics), so a caller that combines several shards
     // into one buffer passes zero_first = false and zeroes it once itself
     if (zero_first) CU(cudaMemsetAsync(d_out, 0, g.row_bytes, st));
@@ -642,11 +650,14 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
         ap.row_bytes = g.row_bytes;
         fill_answer_split(db, g, &ap, throughput);
         ap.out = (uint32_t*)d_out;
-        if (arrivals && signalled && !getenv("PIRB_SIGNAL_KERNEL")) {
-            if (!db->d_cta_done) {
-                CU(cudaMalloc(&db->d_cta_done, kCtaDoneRing * sizeof(uint32_t)));
-                CU(cudaMemset(db->d_cta_done, 0, kCtaDoneRing * sizeof(uint32_t)));
-            }
+        if (((arrivals && signalled) || host_out) && !db->d_cta_done) {
+            CU(cudaMalloc(&db->d_cta_done, kCtaDoneRing * sizeof(uint32_t)));
+            CU(cudaMemset(db->d_cta_done, 0, kCtaDoneRing * sizeof(uint32_t)));
+        }
+        if (host_out) {  // (the caller has checked that this branch will be taken: host_fast_path)
+            ap.host_out = host_out;
+            ap.cta_done = db->d_cta_done + (db->cta_done_next++ % kCtaDoneRing);
+        } else if (arrivals && signalled && !getenv("PIRB_SIGNAL_KERNEL")) {
             ap.arrivals = arrivals;
             ap.cta_done = db->d_cta_done + (db->cta_done_next++ % kCtaDoneRing);  // reset by the launch's last CTA
             *signalled = true;
@@ -961,6 +972,22 @@ extern "C" int pir_answer_batch(pir_db* db, const pir_query* qs, uint32_t n_quer
         if (qs[i].group_size != qs[0].group_size || qs[i].is_keyword != qs[0].is_keyword)
             return fail(PIR_ERR_BAD_ARG, "all queries of a batch must share group_size and is_keyword");
     }
+    // One index query answered by the warp-specialised kernel: its last CTA writes the answer straight into the pinned
+    // host buffer and re-zeroes the device accumulator, so the call is one launch and one stream synchronisation.
+    static const bool no_fast = getenv("PIRB_HOST_COPY_PATH") != nullptr;  // development aid: memset + kernel + copy
+    const bool v1 = getenv("PIRB_KERNEL") && !strcmp(getenv("PIRB_KERNEL"), "v1");
+    if (n_queries == 1 && !no_fast && !v1 && db->h_out_dev && !qs[0].is_keyword && g0.n_rows != 0 &&
+        answer_kernel_supports(g0.row_bytes, 0) && !getenv("PIRB_PHASE_DEBUG")) {
+        if (!db->out_zeroed) CU(cudaMemsetAsync(db->d_out, 0, db->out_cap, db->stream));
+        db->out_zeroed = false;
+        rc = enqueue_answer(db, &qs[0], g0, db->d_out, db->stream, /*zero_first=*/false, nullptr, nullptr, false, db->h_out_dev);
+        if (cudaStreamSynchronize(db->stream) != cudaSuccess && rc == PIR_OK) rc = fail(PIR_ERR_CUDA, "answer kernel failed: %s", cudaGetErrorString(cudaGetLastError()));
+        if (rc) return rc;
+        db->out_zeroed = true;
+        compact_answer(db, g0.W, db->h_out, (uint8_t*)out);
+        return PIR_OK;
+    }
+    db->out_zeroed = false;
     if (batch_uses_bits_path(db, qs, n_queries, g0)) {
         if ((rc = enqueue_batch_bits(db, qs, n_queries, g0, db->d_out, db->stream))) {
             cudaStreamSynchronize(db->stream);
@@ -1072,6 +1099,7 @@ extern "C" int pir_answer_with_bits(pir_db* db, uint32_t group_size, const uint8
     const uint64_t row_bytes = (uint64_t)group_size * db->pitch;
     if ((rc = ensure_out(db, row_bytes))) return rc;
     if ((rc = ensure_bits(db, n_rows ? n_rows : 1))) return rc;
+    db->out_zeroed = false;
     CU(cudaMemsetAsync(db->d_out, 0, row_bytes, db->stream));
     if (n_rows) {
         CU(cudaMemcpyAsync(db->d_bits, bits, n_rows, cudaMemcpyHostToDevice, db->stream));

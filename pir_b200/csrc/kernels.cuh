@@ -53,6 +53,10 @@ struct AnswerPlan {
     // partial has been XORed into `out` (which may be peer memory); cta_done is a zeroed counter in local memory
     uint32_t* arrivals;
     uint32_t* cta_done;
+    // single-GPU host call (optional): the launch's last CTA moves the finished answer from `out` to this mapped
+    // pinned host buffer and leaves `out` zeroed for the next query -- no memset before and no copy after the kernel.
+    // Needs cta_done; not combined with `arrivals`.
+    uint32_t* host_out;
 };
 
 // Batched scan (batch_scan.cu): rows [0, n_rows) of a shard against n_queries packed bit vectors.
