@@ -259,6 +259,30 @@ def test_batch_paths_are_repeatable(gpu_lib, monkeypatch, db_size, slot_bytes, W
                 assert np.array_equal(got, want), (rep, mode)
 
 
+@pytest.mark.parametrize("top_warp", ["1", "0"])
+@pytest.mark.parametrize("split", [("1", "0"), ("2", "1")])
+def test_several_tasks_per_cta_with_and_without_top_walker(gpu_lib, monkeypatch, top_warp, split):
+    """A shard cut into several tasks per CTA (binary split forced through the development switches): the tops of the
+    tasks ahead are walked by the last scan warp (TopWalker, answer_kernel.cu) or by the tree warps themselves; both
+    must give the oracle's bytes for both shares.  (The shipped splits of the small test databases are one task per
+    CTA, so without this test the walker would only run on databases of 2^26 rows and more.)"""
+    db_size, slot_bytes = 1 << 19, 128
+    monkeypatch.setenv("PIRB_DFS_DEPTH", split[0])
+    monkeypatch.setenv("PIRB_DMIN", split[1])
+    monkeypatch.setenv("PIRB_TOP_WARP", top_warp)
+    data = oracle.synth_fill(33, 0, db_size, slot_bytes)
+    with Handle(db_size, slot_bytes) as h:
+        h.fill(33)
+        for k, idx in enumerate((0, 123457, db_size - 1)):
+            os_, qs = make_queries(40 + k, db_size, 1, idx)
+            shares = []
+            for o, q in zip(os_, qs):
+                got = np.asarray(h.answer(q)).reshape(-1)
+                assert np.array_equal(got, np.asarray(oracle.answer(o, data, db_size, slot_bytes, use_tree=True)).reshape(-1)), (idx, top_warp)
+                shares.append(got)
+            assert np.array_equal(shares[0] ^ shares[1], data[idx])
+
+
 @pytest.mark.parametrize("kind", ["dense_sorted", "duplicates", "unsorted", "clustered", "wide64"])
 def test_keyword_prefix_sharing_kernel_matches_oracle(gpu_lib, monkeypatch, kind):
     """The keyword path restarts each row's walk below the last node it shares with the previous row
