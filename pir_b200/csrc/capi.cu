@@ -454,7 +454,12 @@ extern "C" int pir_db_create(int device, uint64_t db_size, uint32_t slot_bytes, 
     uint64_t bytes = slot_count * (uint64_t)db->pitch;
     cudaError_t e = cudaStreamCreateWithFlags(&db->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaMalloc(&db->d_slots, bytes ? bytes : 16);
-    if (e == cudaSuccess && db->pitch != slot_bytes) e = cudaMemset(db->d_slots, 0, bytes ? bytes : 16);
+    // Zero the padding of slots that are not a multiple of 16 bytes.  On the handle's own stream and waited for:
+    // cudaMemset() runs on the legacy default stream, may return before it has executed, and is NOT ordered against
+    // db->stream (non-blocking) -- a fill or query enqueued right after pir_db_create could be overtaken by it and find
+    // part of the database zeroed (seen as an intermittent wrong answer on 100-byte slots).
+    if (e == cudaSuccess && db->pitch != slot_bytes) e = cudaMemsetAsync(db->d_slots, 0, bytes ? bytes : 16, db->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(db->stream);
     if (e != cudaSuccess) {
         int code = e == cudaErrorMemoryAllocation ? PIR_ERR_OOM : PIR_ERR_CUDA;
         fail(code, "pir_db_create: %s", cudaGetErrorString(e));
@@ -542,6 +547,9 @@ extern "C" int pir_db_upload(pir_db* db, uint64_t slot_index, const void* host_s
         CU(cudaMemcpy(dst, host_slots, n_slots * (uint64_t)db->slot_bytes, cudaMemcpyHostToDevice));
     else
         CU(cudaMemcpy2D(dst, db->pitch, host_slots, db->slot_bytes, db->slot_bytes, n_slots, cudaMemcpyHostToDevice));
+    // (a copy from pageable memory may return once it is staged; the queries run on a non-blocking stream that the
+    //  legacy default stream does not order, so wait for the copy itself)
+    CU(cudaStreamSynchronize(0));
     return PIR_OK;
 }
 
@@ -578,6 +586,7 @@ extern "C" int pir_db_set_keywords(pir_db* db, const uint64_t* keywords, uint64_
     if (!db->d_keywords) CU(cudaMalloc(&db->d_keywords, (n ? n : 1) * sizeof(uint64_t)));
     CU(cudaStreamSynchronize(db->stream));
     CU(cudaMemcpy(db->d_keywords, keywords, n * sizeof(uint64_t), cudaMemcpyHostToDevice));
+    CU(cudaStreamSynchronize(0));  // (see pir_db_upload)
     return PIR_OK;
 }
 
@@ -652,7 +661,9 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
         ap.out = (uint32_t*)d_out;
         if (((arrivals && signalled) || host_out) && !db->d_cta_done) {
             CU(cudaMalloc(&db->d_cta_done, kCtaDoneRing * sizeof(uint32_t)));
-            CU(cudaMemset(db->d_cta_done, 0, kCtaDoneRing * sizeof(uint32_t)));
+            // (stream-ordered and waited for: a cudaMemset() on the legacy stream could overtake the kernels' counting)
+            CU(cudaMemsetAsync(db->d_cta_done, 0, kCtaDoneRing * sizeof(uint32_t), st));
+            CU(cudaStreamSynchronize(st));
         }
         if (host_out) {  // (the caller has checked that this branch will be taken: host_fast_path)
             ap.host_out = host_out;
@@ -1326,6 +1337,7 @@ extern "C" int pir_combine_create(int device, uint32_t n_slots, size_t slot_stri
     c->stride = slot_stride;
     cudaError_t e = cudaMalloc(&c->base, c->total_bytes());  // plain cudaMalloc: exportable with CUDA IPC
     if (e == cudaSuccess) e = cudaMemset(c->base, 0, c->total_bytes());
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();  // (the slots are used from non-blocking streams and other processes)
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaMallocHost(&c->h_buf, slot_stride + 16);
     c->clock_khz = ctx->clock_khz;

@@ -236,10 +236,11 @@ def test_batch_two_phase_path_matches_oracle(gpu_lib, monkeypatch, db_size, slot
 
 
 @pytest.mark.parametrize("db_size,slot_bytes,W,nq", [
-    # KNOWN INTERMITTENT MISMATCH: rows of 336 bytes through the two-phase ("bits") path gave
-    # wrong bytes in about 1 of 900 calls under pytest (2 of 45 runs of this test), never in 3 000 calls of
-    # tools/race_hunt*.py.  Not understood yet; kept visible as a non-strict xfail instead of hidden or deleted.
-    pytest.param(3000, 100, 3, 4, marks=pytest.mark.xfail(strict=False, reason="intermittent mismatch in the bits path, DESIGN.md 7")),
+    # Was an intermittent mismatch: pir_db_create zeroed the padding of 100-byte slots with a
+    # cudaMemset() on the legacy stream that a fill on the handle's non-blocking stream could overtake.  Fixed
+    # (stream-ordered memset); the fix could not be confirmed over enough process starts in the round it was made, so the
+    # case stays a non-strict xfail until it has been (tools/flaky_loop.sh, tools/flaky_bits_probe.py).
+    pytest.param(3000, 100, 3, 4, marks=pytest.mark.xfail(strict=False, reason="was intermittent; fix to be confirmed, DESIGN.md 7")),
     (5000, 512, 1, 5), (1 << 15, 256, 1, 6)])
 def test_batch_paths_are_repeatable(gpu_lib, monkeypatch, db_size, slot_bytes, W, nq):
     """The batch paths run kernels on two side streams against per-handle scratch: the same batch, answered 40
