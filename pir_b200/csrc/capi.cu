@@ -131,6 +131,7 @@ int device_ctx(int device, DeviceCtx** out) {
         CU(cudaDeviceGetAttribute(&c.clock_khz, cudaDevAttrClockRate, device));
         CU(cudaMalloc(&c.d_t0, 1024));
         CU(cudaMemcpy(c.d_t0, aes_host().t0, 1024, cudaMemcpyHostToDevice));
+        CU(cudaStreamSynchronize(0));  // small pageable copies return once staged; the kernels run on non-blocking streams
         CU(configure_kernels());
         CU(probe_smem_base(&c.smem_base));
         if (c.smem_base >= 8192) return fail(PIR_ERR_CUDA, "unexpected dynamic shared memory base %u", c.smem_base);
