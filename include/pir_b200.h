@@ -101,6 +101,20 @@ int pir_db_fill_synthetic(pir_db* db, uint64_t seed);
 int pir_db_set_keywords(pir_db* db, const uint64_t* keywords, uint64_t n);
 uint32_t pir_db_slot_pitch(const pir_db* db);
 int pir_db_device(const pir_db* db);
+/*
+ * Path selection and work-split overrides, for tests and measurements.  The library reads NO environment
+ * variable; these options are the only switches it has, and every combination of them gives bit-identical
+ * answers (the test-suite runs the paths against each other and against the oracle).  Defaults are the
+ * measured optimum.  Names (value range; default first):
+ *   dfs_depth (-1 = cost model, 0..7), hi_warps (-1, 4|8|12|16), dmin (-1, 0..7)   work split of the answer kernel
+ *   top_warp (-1 = by row size, 0, 1)     the last scan warp walks the tops of the tasks ahead
+ *   slice_log (0 = by task depth, 2, 3)   rows per thread per hand-off slice (log2)
+ *   batch_mode (0 = by row size, 1 = one fused launch per query, 2 = bit vectors + one scan pass)
+ *   batch_one_stream, batch_latency_split, host_copy_path, signal_kernel, serial_launch (0, 1)
+ *   kernel_v1, expand_v1, keyword_v1, force_unfused (0, 1)   the older two-launch / per-row kernels
+ * PIR_ERR_BAD_ARG for an unknown name or a value out of range.
+ */
+int pir_db_set_option(pir_db* db, const char* name, int64_t value);
 
 /* ---- the answer path -------------------------------------------------------------------------- */
 /*
@@ -154,6 +168,8 @@ int pir_server_fill_synthetic(pir_server* s, uint64_t seed);
 /* Database.SetKeywords (db.go:392-394) for the whole database: n must equal db_size; shard g keeps
  * keywords[slot_begin_g, +slot_count_g).  Keyword queries (db.go:119-121,132-135) need group_size 1 here. */
 int pir_server_set_keywords(pir_server* s, const uint64_t* keywords, uint64_t n);
+/* pir_db_set_option on every shard. */
+int pir_server_set_option(pir_server* s, const char* name, int64_t value);
 /* PrivateSecretSharedQuery (db.go:68-72) over all shards: out gets group_size*slot_bytes bytes. */
 int pir_server_answer(pir_server* s, const pir_query* q, void* out, size_t out_len);
 int pir_server_answer_batch(pir_server* s, const pir_query* qs, uint32_t n_queries, void* out, size_t out_len);

@@ -9,6 +9,7 @@ import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libpir_b200.so")
+DEV_LIB_PATH = os.path.join(_HERE, "lib", "libpir_b200_dev.so")   # `make dev`: instrumentation for tools/ only
 CSRC_DIR = os.path.join(_HERE, "csrc")
 
 PIR_MAX_NUM_BITS = 64
@@ -26,13 +27,13 @@ PIR_ERR_UNSUPPORTED = -5
 EXPORTS = [
     "pir_abi_version", "pir_last_error", "pir_device_count",
     "pir_db_create", "pir_db_destroy", "pir_db_upload", "pir_db_download", "pir_db_fill_synthetic",
-    "pir_db_set_keywords", "pir_db_slot_pitch", "pir_db_device", "pir_db_rows",
+    "pir_db_set_keywords", "pir_db_slot_pitch", "pir_db_device", "pir_db_rows", "pir_db_set_option",
     "pir_answer", "pir_answer_batch", "pir_expand_bits", "pir_answer_with_bits",
     "pir_answer_batch_device", "pir_dpf_eval_points", "pir_xor_combine", "pir_num_bits_for",
     "pir_kernel_launch_count", "pir_client_gen_two_server",
     "pir_db_set_kernel_timing", "pir_db_get_kernel_timing",
     "pir_server_create", "pir_server_destroy", "pir_server_num_shards", "pir_server_shard",
-    "pir_server_upload", "pir_server_fill_synthetic", "pir_server_set_keywords", "pir_server_answer", "pir_server_answer_batch",
+    "pir_server_upload", "pir_server_fill_synthetic", "pir_server_set_keywords", "pir_server_set_option", "pir_server_answer", "pir_server_answer_batch",
     "pir_combine_create", "pir_combine_export", "pir_combine_open", "pir_combine_destroy",
     "pir_combine_reset", "pir_answer_accumulate_device", "pir_combine_wait_read", "pir_combine_slot_ptr",
     "pir_audit_shared_query", "pir_audit_shared_query_with_bits",
@@ -75,9 +76,18 @@ class PirError(RuntimeError):
         self.code = code
 
 
+def use_dev_library():
+    """tools/ only: load the -DPIRB_DEV build (in-kernel phase counters, PIRB_* environment switches)."""
+    global LIB_PATH, _lib
+    if _lib is not None:
+        raise RuntimeError("the library is already loaded")
+    subprocess.check_call(["make", "-C", CSRC_DIR, "-s", "-j8", "dev"])
+    LIB_PATH = DEV_LIB_PATH
+
+
 def build(force=False, extra=""):
     """Compile the CUDA library for sm_100a (nvcc cross-compiles without a GPU)."""
-    args = ["make", "-C", CSRC_DIR, "-s"]
+    args = ["make", "-C", CSRC_DIR, "-s", "-j8"]
     if force:
         args.append("-B")
     if extra:
@@ -113,6 +123,8 @@ def lib():
     L.pir_db_slot_pitch.restype = C.c_uint32
     L.pir_db_device.argtypes = [vp]
     L.pir_db_rows.argtypes = [vp, C.c_uint32, u64p, u64p]
+    L.pir_db_set_option.argtypes = [vp, C.c_char_p, C.c_int64]
+    L.pir_server_set_option.argtypes = [vp, C.c_char_p, C.c_int64]
     L.pir_answer.argtypes = [vp, qp, vp, C.c_size_t]
     L.pir_answer_batch.argtypes = [vp, qp, C.c_uint32, vp, C.c_size_t]
     L.pir_expand_bits.argtypes = [vp, qp, u8p, C.c_uint64]

@@ -179,7 +179,7 @@ __device__ __forceinline__ void scan_group(const AnswerPlan& ap, const ScanLane&
 #pragma unroll
     for (int cb = 0; cb < NCB; cb++) {
         const uint8_t* cbase = gbase + cb * 512;
-        for (uint32_t e0 = 0; e0 < ((ap.pad & 1u) ? 0u : total); e0 += sl.rpl * UNROLL) {
+        for (uint32_t e0 = 0; e0 < ((PIRB_AP_PAD(ap) & 1u) ? 0u : total); e0 += sl.rpl * UNROLL) {
             uint4 v[UNROLL];
 #pragma unroll
             for (int k = 0; k < UNROLL / 8; k++) {
@@ -619,7 +619,7 @@ __device__ __forceinline__ void consume_slices(const QueryConst& qc, const Answe
 #pragma unroll
     for (int cb = 0; cb < NCB; cb++) acc[cb] = make_uint4(0, 0, 0, 0);
     long long c_wait = 0;
-    const long long c_in = ap.dbg ? clock64() : 0;
+    const long long c_in = PIRB_AP_DBG(ap) ? clock64() : 0;
     // DUAL: this scan warp also walks the tops of the tasks ahead (TopWalker), before anything else whenever a
     // hand-over buffer is free -- the tree warps will wait for it at the next task boundary, the scan has slack.
     while (true) {
@@ -638,7 +638,7 @@ __device__ __forceinline__ void consume_slices(const QueryConst& qc, const Answe
         }
         if (!have) break;
         const uint32_t slot = gsl & (kRing - 1u), par = (gsl / kRing) & 1u;
-        const long long cw0 = (ap.dbg && warp_in_cta == kTreeWarps) ? clock64() : 0;
+        const long long cw0 = (PIRB_AP_DBG(ap) && warp_in_cta == kTreeWarps) ? clock64() : 0;
         if (DUAL) {
             // This warp also walks the tops of the tasks ahead, before anything else whenever a hand-over buffer is
             // free: the tree warps will wait for it at the next task boundary, the scan has slack.  The slice just
@@ -650,7 +650,7 @@ __device__ __forceinline__ void consume_slices(const QueryConst& qc, const Answe
             }
         }
         mbar_wait(full_bar(slot), par);
-        if (ap.dbg && warp_in_cta == kTreeWarps) c_wait += clock64() - cw0;
+        if (PIRB_AP_DBG(ap) && warp_in_cta == kTreeWarps) c_wait += clock64() - cw0;
         uint64_t grow0;
         uint32_t rows_log, gslog;
         {
@@ -671,8 +671,8 @@ __device__ __forceinline__ void consume_slices(const QueryConst& qc, const Answe
         }
     }
     // (DUAL: no top can be pending here -- units run out only once the tree warps are in the CTA's last task)
-    if (ap.dbg && warp_in_cta == kTreeWarps && lane == 0) {  // first scan warp: cycles scanning vs waiting for slices
-        ap.dbg[11264ull + blockIdx.x] = ((unsigned long long)(clock64() - c_in - c_wait) << 32) | (unsigned long long)(c_wait & 0xffffffffll);
+    if (PIRB_AP_DBG(ap) && warp_in_cta == kTreeWarps && lane == 0) {  // first scan warp: cycles scanning vs waiting for slices
+        PIRB_AP_DBG(ap)[11264ull + blockIdx.x] = ((unsigned long long)(clock64() - c_in - c_wait) << 32) | (unsigned long long)(c_wait & 0xffffffffll);
     }
     fold_acc<NCB>(sl, acc);
 }
@@ -696,10 +696,10 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
     const uint32_t n_tasks = ti.n;
     uint32_t it = 0;
     uint32_t gs = 0;  // slices published so far (ring position)
-    long long c_top = 0, c_bfs = 0, c_dfs = 0, c_tail = 0, c_pub = 0, c_mark = clock64();
+    long long c_top = 0, c_bfs = 0, c_dfs = 0, c_tail = 0, c_pub = 0, c_mark = PIRB_AP_DBG(ap) ? clock64() : 0;
     const long long c_begin = c_mark;
 #define PHASE(acc)                              \
-    if (ap.dbg && tid == 0) {                   \
+    if (PIRB_AP_DBG(ap) && tid == 0) {                   \
         const long long now_ = clock64();       \
         acc += now_ - c_mark;                   \
         c_mark = now_;                          \
@@ -762,7 +762,7 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
                 cp = cp < Ls ? cp : Ls;
             }
             if (warp == 0u) {  // one warp walks the whole chain, the node stays in registers (no CTA barrier per level)
-                quad_path_walk(qc, lc, a, L, cp, Ls, path_s, path_t, (ap.dbg && blockIdx.x == 0 && it == 0) ? ap.dbg : nullptr);
+                quad_path_walk(qc, lc, a, L, cp, Ls, path_s, path_t, (PIRB_AP_DBG(ap) && blockIdx.x == 0 && it == 0) ? PIRB_AP_DBG(ap) : nullptr);
                 if (lane == 0) {
                     bfs_s[(Ls & 1u) * kTreeThreads] = path_s[Ls];
                     bfs_t[(Ls & 1u) * kTreeThreads] = path_t[Ls];
@@ -854,9 +854,9 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
 #define PUBLISH(word_)                                                              \
     {                                                                               \
         const uint32_t slot_ = gs & (kRing - 1u), par_ = (gs / kRing) & 1u;         \
-        const long long w0_ = (ap.dbg && tid == 0) ? clock64() : 0;                 \
+        const long long w0_ = (PIRB_AP_DBG(ap) && tid == 0) ? clock64() : 0;                 \
         mbar_wait(empty_bar(slot_), par_ ^ 1u);                                     \
-        if (ap.dbg && tid == 0) c_pub += clock64() - w0_;                           \
+        if (PIRB_AP_DBG(ap) && tid == 0) c_pub += clock64() - w0_;                           \
         ring_words(slot_)[tid] = (word_);                                           \
         __syncwarp();                                                               \
         if (lane == 0) mbar_arrive(full_bar(slot_));                                \
@@ -923,21 +923,21 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
 #undef PUBLISH
         PHASE(c_dfs)
     }
-    if (ap.dbg && lane == 0) {  // spread of the tree warps' finishing times within the CTA
+    if (PIRB_AP_DBG(ap) && lane == 0) {  // spread of the tree warps' finishing times within the CTA
         const unsigned long long te = (unsigned long long)(clock64() - c_entry);
-        atomicMax(ap.dbg + 8192ull + 2ull * blockIdx.x, te);
-        atomicMax(ap.dbg + 8192ull + 2ull * blockIdx.x + 1ull, (1ull << 40) - te);
+        atomicMax(PIRB_AP_DBG(ap) + 8192ull + 2ull * blockIdx.x, te);
+        atomicMax(PIRB_AP_DBG(ap) + 8192ull + 2ull * blockIdx.x + 1ull, (1ull << 40) - te);
         // scan backlog at that moment: units published minus units claimed
         const uint32_t claimed = *reinterpret_cast<volatile uint32_t*>(g_smem2 + (kAbsClaim - smem_addr(g_smem2)));
         const uint32_t total_u = gs * kGroups;
-        atomicMax(ap.dbg + 10240ull + blockIdx.x, (unsigned long long)(total_u > claimed ? total_u - claimed : 0u) + 1ull);
+        atomicMax(PIRB_AP_DBG(ap) + 10240ull + blockIdx.x, (unsigned long long)(total_u > claimed ? total_u - claimed : 0u) + 1ull);
     }
     // nothing left to expand: help the scan warps drain the ring
     if constexpr (NCB != 0) consume_slices<NCB>(qc, ap, warp, false);
     PHASE(c_tail)
 #undef PHASE
-    if (ap.dbg && tid == 0) {
-        unsigned long long* o = ap.dbg + 8ull * blockIdx.x;
+    if (PIRB_AP_DBG(ap) && tid == 0) {
+        unsigned long long* o = PIRB_AP_DBG(ap) + 8ull * blockIdx.x;
         o[0] = (unsigned long long)c_top; o[1] = (unsigned long long)c_bfs; o[2] = (unsigned long long)c_pub;
         o[3] = (unsigned long long)c_dfs; o[4] = (unsigned long long)c_tail; o[5] = (unsigned long long)(clock64() - c_begin);
         o[6] = it; o[7] = (unsigned long long)(c_begin - c_entry);
@@ -949,11 +949,11 @@ __global__ void __launch_bounds__(kAnswerThreads, 1)
 answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ AnswerPlan ap,
               const uint32_t* __restrict__ t0) {
     const uint32_t base = smem_addr(g_smem2);
-    const long long c_entry = clock64();
-    if (ap.dbg && threadIdx.x == 0) {  // CTA start on the GPU-wide timer (ns): launch stagger across SMs
+    const long long c_entry = PIRB_AP_DBG(ap) ? clock64() : 0;
+    if (PIRB_AP_DBG(ap) && threadIdx.x == 0) {  // CTA start on the GPU-wide timer (ns): launch stagger across SMs
         unsigned long long gt;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
-        ap.dbg[12288ull + blockIdx.x] = gt;
+        PIRB_AP_DBG(ap)[12288ull + blockIdx.x] = gt;
     }
     {
         uint32_t dyn;
@@ -1029,12 +1029,12 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
             }
         }
     }
-    if (ap.dbg) {
+    if (PIRB_AP_DBG(ap)) {
         __syncthreads();
         if (threadIdx.x == 0) {
             unsigned long long gt;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
-            ap.dbg[13312ull + blockIdx.x] = gt;
+            PIRB_AP_DBG(ap)[13312ull + blockIdx.x] = gt;
         }
     }
 }
@@ -1085,7 +1085,7 @@ cudaError_t launch_answer(const QueryConst& qc, const AnswerPlan& ap, const uint
     const size_t smem = kSmemEnd - smem_base;
     // two code paths per row geometry: keys with an odd FinalCW need the leaves' control bits, keys with an
     // even one do not (aes_unrolled.cuh, leaf_parent_tail_even)
-    const bool odd = qc.fcw_parity != 0 || (ap.pad & 2u);
+    const bool odd = qc.fcw_parity != 0 || (PIRB_AP_PAD(ap) & 2u);
 #define PIRB_LAUNCH(NCB)                                                                           \
     do {                                                                                           \
         if (odd)                                                                                   \

@@ -11,6 +11,14 @@
 #include <new>
 #include <vector>
 
+#ifdef PIRB_DEV
+#include "dev_hooks.cuh"
+using pirb_dev::DevPhase;
+static inline bool dev_phase_debug_on() { return pirb_dev::dev_phase_debug(); }
+#else
+static inline bool dev_phase_debug_on() { return false; }
+#endif
+
 using namespace pirb;
 
 // ---- errors -------------------------------------------------------------------------------------
@@ -113,6 +121,17 @@ struct DeviceCtx {
 std::mutex g_dev_mu;
 DeviceCtx g_dev[64];
 
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev);
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
 int device_ctx(int device, DeviceCtx** out) {
     int n = pir_device_count();
     if (n <= 0) return fail(PIR_ERR_CUDA, "no CUDA device is visible (this library has no CPU path)");
@@ -120,7 +139,7 @@ int device_ctx(int device, DeviceCtx** out) {
     std::lock_guard<std::mutex> lk(g_dev_mu);
     DeviceCtx& c = g_dev[device];
     if (!c.ready) {
-        CU(cudaSetDevice(device));
+        DeviceGuard guard(device);  // (the caller's current device is restored on every path out of this block)
         cudaDeviceProp prop;
         CU(cudaGetDeviceProperties(&prop, device));
         if (prop.major < 10)
@@ -192,6 +211,22 @@ static int build_query_const(const pir_query* q, uint32_t num_bits, QueryConst* 
 }
 
 // ---- database handle ----------------------------------------------------------------------------
+// Path selection and work-split overrides (pir_db_set_option).  Every combination gives bit-identical answers;
+// the defaults are the measured optimum.  The library reads no environment variable.
+struct Tuning {
+    int dfs_depth = -1;   // uniform / binary split: depth of the deepest per-thread subtree (0..7), -1 = cost model
+    int hi_warps = -1;    // uniform split: 4, 8, 12 or 16 "hi" tree warps, -1 = cost model
+    int dmin = -1;        // binary split: smallest task depth, -1 = cost model
+    int top_warp = -1;    // 1 / 0: the last scan warp walks the tops of the tasks ahead, -1 = by row size
+    int slice_log = 0;    // 2 or 3: log2(rows per thread per slice), 0 = by task depth
+    int batch_mode = 0;   // batches: 0 = by row size, 1 = one fused launch per query, 2 = bit vectors + one scan pass
+    bool batch_one_stream = false, batch_latency_split = false;
+    bool kernel_v1 = false, expand_v1 = false, keyword_v1 = false, force_unfused = false;  // the older kernels
+    bool signal_kernel = false;   // multi-GPU: separate arrival kernel instead of the answer kernel's last CTA
+    bool host_copy_path = false;  // pir_answer: memset + kernel + copy instead of the one-launch host path
+    bool serial_launch = false;   // no programmatic dependent launch between consecutive answer kernels
+};
+
 struct pir_db {
     int device = 0;
     DeviceCtx* ctx = nullptr;
@@ -203,6 +238,7 @@ struct pir_db {
     uint64_t* d_keywords = nullptr;
     cudaStream_t stream = nullptr;
     std::mutex mu;
+    Tuning tune;
     // grow-only scratch
     uint4* d_front_s[2] = {nullptr, nullptr};
     uint8_t* d_front_t[2] = {nullptr, nullptr};
@@ -232,16 +268,6 @@ struct pir_db {
 };
 
 namespace {
-struct DeviceGuard {
-    int prev = -1;
-    explicit DeviceGuard(int dev) {
-        cudaGetDevice(&prev);
-        if (prev != dev) cudaSetDevice(dev);
-    }
-    ~DeviceGuard() {
-        if (prev >= 0) cudaSetDevice(prev);
-    }
-};
 
 int ensure_front(pir_db* db, uint64_t n) {
     if (n <= db->front_cap) return PIR_OK;
@@ -316,13 +342,11 @@ struct Plan {
 };
 
 // Choose the per-thread depth D and CTA breadth B (kernels.cuh) for a shard of rows.
-Plan make_plan(uint32_t nb, uint64_t first_row, uint64_t n_rows, int num_sms, int max_depth = kMaxDfsDepth) {
+Plan make_plan(uint32_t nb, uint64_t first_row, uint64_t n_rows, int num_sms, int forced = -1) {
     Plan best{};
     double best_score = -1.0;
     uint32_t Bmax = nb - 1 < (uint32_t)kFusedLogThreads ? nb - 1 : (uint32_t)kFusedLogThreads;
-    int forced = -1;
-    if (const char* e = getenv("PIRB_DFS_DEPTH")) forced = atoi(e);
-    for (int D = max_depth; D >= 0; D--) {
+    for (int D = kMaxDfsDepth; D >= 0; D--) {
         if ((uint32_t)D + Bmax > nb - 1) continue;
         if (forced >= 0 && D != forced && (uint32_t)forced + Bmax <= nb - 1) continue;
         uint32_t B = Bmax;
@@ -359,25 +383,23 @@ double uniform_task_cost(uint32_t top_bits, uint32_t D, uint32_t hiw) {
 }
 // throughput: many independent launches run back to back on two streams (batches), so a CTA that finishes
 // early is replaced by one of the next launch: total work matters more than the slowest CTA.
-AnswerSplit choose_answer_split(uint32_t nb, uint64_t first_row, uint64_t n_rows, int num_sms, bool throughput = false) {
+AnswerSplit choose_answer_split(uint32_t nb, uint64_t first_row, uint64_t n_rows, int num_sms, bool throughput = false,
+                                const Tuning& tune = Tuning()) {
     AnswerSplit sp{};
     const uint32_t top_bits = nb - 1;
     uint32_t dmax = top_bits > (uint32_t)kFusedLogThreads ? top_bits - (uint32_t)kFusedLogThreads : 0u;
     if (dmax > 7u) dmax = 7u;
-    if (const char* e = getenv("PIRB_DFS_DEPTH")) {
-        const uint32_t f = (uint32_t)atoi(e);
-        if (f < dmax) dmax = f;
-    }
+    if (tune.dfs_depth >= 0 && (uint32_t)tune.dfs_depth < dmax) dmax = (uint32_t)tune.dfs_depth;
     sp.D = dmax;
     sp.hi_warps = 16;
-    // fixed splits (development aids): PIRB_DFS_DEPTH x PIRB_HI_WARPS (uniform), PIRB_DFS_DEPTH / PIRB_DMIN (binary)
-    if (const char* e = getenv("PIRB_HI_WARPS")) {
-        const uint32_t f = (uint32_t)atoi(e);
+    // fixed splits (pir_db_set_option): dfs_depth x hi_warps (uniform), dfs_depth / dmin (binary)
+    if (tune.hi_warps >= 0) {
+        const uint32_t f = (uint32_t)tune.hi_warps;
         if (sp.D > 0 && (f == 4 || f == 8 || f == 12)) sp.hi_warps = f;
         return sp;
     }
-    if (const char* e = getenv("PIRB_DMIN")) {
-        const uint32_t f = (uint32_t)atoi(e);
+    if (tune.dmin >= 0) {
+        const uint32_t f = (uint32_t)tune.dmin;
         sp.hi_warps = 0;
         sp.Dmin = f < sp.D ? f : sp.D;
         return sp;
@@ -455,11 +477,13 @@ extern "C" int pir_db_create(int device, uint64_t db_size, uint32_t slot_bytes, 
     uint64_t bytes = slot_count * (uint64_t)db->pitch;
     cudaError_t e = cudaStreamCreateWithFlags(&db->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaMalloc(&db->d_slots, bytes ? bytes : 16);
-    // Zero the padding of slots that are not a multiple of 16 bytes.  On the handle's own stream and waited for:
+    // Zero the slots (and the padding of slots that are not a multiple of 16 bytes).  On the handle's own stream and waited for:
     // cudaMemset() runs on the legacy default stream, may return before it has executed, and is NOT ordered against
     // db->stream (non-blocking) -- a fill or query enqueued right after pir_db_create could be overtaken by it and find
     // part of the database zeroed (seen as an intermittent wrong answer on 100-byte slots).
-    if (e == cudaSuccess && db->pitch != slot_bytes) e = cudaMemsetAsync(db->d_slots, 0, bytes ? bytes : 16, db->stream);
+    // Every slot starts as zeros, like the reference's make([]byte, n) (slot.go:137-170): a query on a handle that has
+    // been uploaded only in part must not XOR stale device memory into the answer.
+    if (e == cudaSuccess) e = cudaMemsetAsync(db->d_slots, 0, bytes ? bytes : 16, db->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(db->stream);
     if (e != cudaSuccess) {
         int code = e == cudaErrorMemoryAllocation ? PIR_ERR_OOM : PIR_ERR_CUDA;
@@ -523,6 +547,40 @@ extern "C" int pir_db_get_kernel_timing(pir_db* db, double* total_ms, uint64_t* 
     *launches = db->ev_used;
     db->ev_used = 0;
     return PIR_OK;
+}
+
+namespace {
+int set_tuning(Tuning& t, const char* name, int64_t v) {
+    struct { const char* n; int* i; bool* b; int64_t lo, hi; } tab[] = {
+        {"dfs_depth", &t.dfs_depth, nullptr, -1, 7},   {"hi_warps", &t.hi_warps, nullptr, -1, 16},
+        {"dmin", &t.dmin, nullptr, -1, 7},             {"top_warp", &t.top_warp, nullptr, -1, 1},
+        {"slice_log", &t.slice_log, nullptr, 0, 3},    {"batch_mode", &t.batch_mode, nullptr, 0, 2},
+        {"batch_one_stream", nullptr, &t.batch_one_stream, 0, 1},
+        {"batch_latency_split", nullptr, &t.batch_latency_split, 0, 1},
+        {"kernel_v1", nullptr, &t.kernel_v1, 0, 1},    {"expand_v1", nullptr, &t.expand_v1, 0, 1},
+        {"keyword_v1", nullptr, &t.keyword_v1, 0, 1},  {"force_unfused", nullptr, &t.force_unfused, 0, 1},
+        {"signal_kernel", nullptr, &t.signal_kernel, 0, 1},
+        {"host_copy_path", nullptr, &t.host_copy_path, 0, 1},
+        {"serial_launch", nullptr, &t.serial_launch, 0, 1},
+    };
+    for (auto& e : tab) {
+        if (strcmp(e.n, name)) continue;
+        if (v < e.lo || v > e.hi) return fail(PIR_ERR_BAD_ARG, "option %s: value %lld outside [%lld, %lld]", name, (long long)v,
+                                              (long long)e.lo, (long long)e.hi);
+        if (e.i) *e.i = (int)v;
+        else *e.b = v != 0;
+        return PIR_OK;
+    }
+    return fail(PIR_ERR_BAD_ARG, "unknown option '%s'", name);
+}
+}  // namespace
+
+extern "C" int pir_db_set_option(pir_db* db, const char* name, int64_t value) {
+    if (!db || !name) return fail(PIR_ERR_BAD_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(db->mu);
+    int rc = set_tuning(db->tune, name, value);
+    db->split_nb = 0;  // the cached work split may no longer apply
+    return rc;
 }
 
 extern "C" uint32_t pir_db_slot_pitch(const pir_db* db) { return db ? db->pitch : 0; }
@@ -608,6 +666,13 @@ struct QueryGeom {
 void fill_answer_split(pir_db* db, const QueryGeom& g, AnswerPlan* ap, bool throughput = false);
 
 int query_geom(const pir_db* db, const pir_query* q, QueryGeom* g) {
+#ifdef PIRB_DEV
+    {  // DEV build only: the tuning options follow the PIRB_* environment variables, re-read at every query
+        pir_db* mdb = const_cast<pir_db*>(db);
+        pirb_dev::dev_apply_env(mdb->tune);
+        mdb->split_nb = 0;
+    }
+#endif
     if (!q) return fail(PIR_ERR_BAD_ARG, "query is null");
     if (q->reserved != 0) return fail(PIR_ERR_BAD_ARG, "pir_query.reserved must be 0");
     g->W = q->group_size;
@@ -643,7 +708,7 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
         if (g.first_row < db->slot_begin || g.first_row + g.n_rows > db->slot_begin + db->slot_count)
             return fail(PIR_ERR_BAD_ARG, "keyword queries with group_size > 1 need an unsharded handle");
         if ((rc = ensure_bits(db, g.n_rows))) return rc;
-        if (getenv("PIRB_KEYWORD_V1"))
+        if (db->tune.keyword_v1)
             CU(launch_eval_points(qc, db->d_keywords + (g.first_row - db->slot_begin), 0, g.n_rows, nullptr,
                                   db->d_bits, ctx.d_t0, ctx.smem_base, st));
         else
@@ -652,8 +717,7 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
         CU(launch_scan_bytes(db->d_slots, g.row_bytes, g.n_rows, db->d_bits, (uint32_t*)d_out, ctx.num_sms, st));
         return PIR_OK;
     }
-    static const bool use_v1 = getenv("PIRB_KERNEL") && !strcmp(getenv("PIRB_KERNEL"), "v1");
-    if (!use_v1 && answer_kernel_supports(g.row_bytes, 0)) {
+    if (!db->tune.kernel_v1 && answer_kernel_supports(g.row_bytes, 0)) {
         // warp-specialised kernel: walks the top of the tree itself, one launch per query
         AnswerPlan ap{};
         ap.db = db->d_slots;
@@ -669,19 +733,15 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
         if (host_out) {  // (the caller has checked that this branch will be taken: host_fast_path)
             ap.host_out = host_out;
             ap.cta_done = db->d_cta_done + (db->cta_done_next++ % kCtaDoneRing);
-        } else if (arrivals && signalled && !getenv("PIRB_SIGNAL_KERNEL")) {
+        } else if (arrivals && signalled && !db->tune.signal_kernel) {
             ap.arrivals = arrivals;
             ap.cta_done = db->d_cta_done + (db->cta_done_next++ % kCtaDoneRing);  // reset by the launch's last CTA
             *signalled = true;
         }
-        if (const char* dbg = getenv("PIRB_DEBUG_FLAGS")) ap.pad = (uint32_t)atoi(dbg);  // timing experiments only
-        static const bool phase_debug = getenv("PIRB_PHASE_DEBUG") != nullptr;
-        unsigned long long* d_dbg = nullptr;
-        if (phase_debug) {
-            CU(cudaMalloc(&d_dbg, 8 * 15 * 1024));
-            CU(cudaMemsetAsync(d_dbg, 0, 8 * 15 * 1024, st));
-            ap.dbg = d_dbg;
-        }
+#ifdef PIRB_DEV
+        DevPhase dev_phase;
+        if (int drc = dev_phase.begin(&ap, st)) return drc;
+#endif
         cudaEvent_t e0 = nullptr, e1 = nullptr;
         if (db->timing) {
             if (db->ev_used == db->ev_pool.size()) {
@@ -696,60 +756,12 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
         }
         CU(launch_answer(qc, ap, ctx.d_t0, ctx.smem_base, ctx.num_sms, st));
         if (e1) CU(cudaEventRecord(e1, st));
-        if (d_dbg) {  // development aid: average per-CTA cycles per phase of the tree warps, to stderr
-            std::vector<unsigned long long> h(15 * 1024);
-            CU(cudaStreamSynchronize(st));
-            CU(cudaMemcpy(h.data(), d_dbg, 8 * 15 * 1024, cudaMemcpyDeviceToHost));
-            cudaFree(d_dbg);
-            double sum[8] = {0}, mx = 0;
-            int n = 0;
-            for (int b = 0; b < 1024; b++) {
-                if (!h[8 * b + 5]) continue;
-                n++;
-                for (int k = 0; k < 8; k++) sum[k] += (double)h[8 * b + k];
-                if ((double)(h[8 * b + 5] + h[8 * b + 7]) > mx) mx = (double)(h[8 * b + 5] + h[8 * b + 7]);
-            }
-            unsigned long long g0 = ~0ull, g1 = 0, gs_last = 0, ge_first = ~0ull;
-            for (int b = 0; b < 1024; b++)
-                if (h[8 * b + 5]) {
-                    if (h[12288 + b] < g0) g0 = h[12288 + b];
-                    if (h[12288 + b] > gs_last) gs_last = h[12288 + b];
-                    if (h[13312 + b] > g1) g1 = h[13312 + b];
-                    if (h[13312 + b] < ge_first) ge_first = h[13312 + b];
-                }
-            if (getenv("PIRB_PHASE_DEBUG")[0] == '3')
-                for (int l = 1; l < 64; l++)
-                    if (h[14336 + l] && h[14336 + l - 1]) fprintf(stderr, "[top cta0] level %d took %llu cycles\n", l, h[14336 + l] - h[14336 + l - 1]);
-            if (n) fprintf(stderr, "[phase] globaltimer: first CTA start to last CTA start %llu ns, first CTA end at %llu ns, last CTA end at %llu ns\n",
-                           gs_last - g0, ge_first - g0, g1 - g0);
-            if (getenv("PIRB_PHASE_DEBUG")[0] == '2')
-                for (int b = 0; b < 1024; b++)
-                    if (h[8 * b + 5])
-                        fprintf(stderr, "[cta %d] tasks %llu prologue %llu top %llu bfs %llu dfs %llu tail %llu total %llu start_ns %llu end_ns %llu\n", b, h[8 * b + 6],
-                                h[8 * b + 7], h[8 * b + 0], h[8 * b + 1], h[8 * b + 3], h[8 * b + 4], h[8 * b + 5] + h[8 * b + 7],
-                                h[12288 + b] - g0, h[13312 + b] - g0);
-            double spread = 0;
-            for (int b = 0; b < 1024; b++)
-                if (h[8 * b + 5]) spread += (double)h[8192 + 2 * b] - (double)((1ull << 40) - h[8192 + 2 * b + 1]);
-            double busy = 0, waitc = 0;
-            for (int b = 0; b < 1024; b++)
-                if (h[8 * b + 5]) {
-                    busy += (double)(h[11264 + b] >> 32);
-                    waitc += (double)(h[11264 + b] & 0xffffffffull);
-                }
-            if (n) fprintf(stderr, "[phase] first scan warp: %.0f cycles scanning, %.0f waiting for slices\n", busy / n, waitc / n);
-            double backlog = 0;
-            for (int b = 0; b < 1024; b++)
-                if (h[8 * b + 5]) backlog += (double)h[10240 + b] - 1.0;
-            if (n) fprintf(stderr, "[phase] scan backlog when a tree warp finishes (max over its warps): %.1f units of 32 words\n", backlog / n);
-            if (n) fprintf(stderr, "[phase] first-to-last tree warp done within a CTA: %.0f cycles (mean)\n", spread / n);
-            if (n)
-                fprintf(stderr, "[phase] ctas %d tasks %.2f | prologue %.0f top %.0f bfs %.0f dfs %.0f (of which ring-full wait %.0f) tail %.0f | tree total %.0f cycles, slowest CTA %.0f\n",
-                        n, sum[6] / n, sum[7] / n, sum[0] / n, sum[1] / n, sum[3] / n, sum[2] / n, sum[4] / n, sum[5] / n, mx);
-        }
+#ifdef PIRB_DEV
+        if (int drc = dev_phase.report(st)) return drc;
+#endif
         return PIR_OK;
     }
-    Plan p = make_plan(g.nb, g.first_row, g.n_rows, ctx.num_sms);
+    Plan p = make_plan(g.nb, g.first_row, g.n_rows, ctx.num_sms, db->tune.dfs_depth);
     if ((rc = ensure_front(db, p.task_count + 2))) return rc;
     TopPlan tp{};
     tp.Fc = p.Fc;
@@ -773,7 +785,7 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
     fp.frontier_s = db->d_front_s[p.Fc & 1];
     fp.frontier_t = db->d_front_t[p.Fc & 1];
     fp.out = (uint32_t*)d_out;
-    const bool fused = fused_supports_row_bytes(g.row_bytes) && !getenv("PIRB_FORCE_UNFUSED");
+    const bool fused = fused_supports_row_bytes(g.row_bytes) && !db->tune.force_unfused;
     if (fused) {
         cudaEvent_t e0 = nullptr, e1 = nullptr;
         if (db->timing) {
@@ -802,7 +814,7 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
 // Fill the work-split fields of an AnswerPlan (cached per handle for the last (num_bits, rows) seen).
 void fill_answer_split(pir_db* db, const QueryGeom& g, AnswerPlan* ap, bool throughput) {
     if (db->split_nb != g.nb || db->split_first != g.first_row || db->split_rows != g.n_rows || db->split_tp != throughput) {
-        const AnswerSplit sp = choose_answer_split(g.nb, g.first_row, g.n_rows, db->ctx->num_sms, throughput);
+        const AnswerSplit sp = choose_answer_split(g.nb, g.first_row, g.n_rows, db->ctx->num_sms, throughput, db->tune);
         db->split_tp = throughput;
         db->split_nb = g.nb;
         db->split_first = g.first_row;
@@ -823,11 +835,8 @@ void fill_answer_split(pir_db* db, const QueryGeom& g, AnswerPlan* ap, bool thro
     // have slack: 2^24 x 256 B in several tasks per CTA 0.943 -> 0.937 ms; with 32-byte rows they have none
     // (2^28 x 32 B: 13.05 ms without the walker, 13.22 ms with it).
     ap->top_warp = g.row_bytes >= 128u ? 1u : 0u;
-    if (const char* e = getenv("PIRB_TOP_WARP")) ap->top_warp = atoi(e) ? 1u : 0u;  // development aid (A/B)
-    if (const char* e = getenv("PIRB_SLICE_LOG")) {  // development aid
-        const uint32_t f = (uint32_t)atoi(e);
-        if (f == 2u || f == 3u) ap->slog_cap = f;
-    }
+    if (db->tune.top_warp >= 0) ap->top_warp = db->tune.top_warp ? 1u : 0u;
+    if (db->tune.slice_log == 2 || db->tune.slice_log == 3) ap->slog_cap = (uint32_t)db->tune.slice_log;
 }
 
 // Should a batch of n index queries go through the two-phase path (bit vectors, then ONE pass over the
@@ -837,11 +846,8 @@ bool batch_uses_bits_path(const pir_db* db, const pir_query* qs, uint32_t n, con
     if (qs[0].is_keyword || g.n_rows == 0) return false;
     uint32_t tpq, segc, sr, qpl;
     if (!batch_scan_geometry(g.row_bytes, &tpq, &segc, &sr, &qpl)) return false;
-    if (const char* e = getenv("PIRB_BATCH_MODE")) {
-        if (!strcmp(e, "fused")) return false;
-        if (!strcmp(e, "bits")) return true;
-    }
-    (void)db;
+    if (db->tune.batch_mode == 1) return false;
+    if (db->tune.batch_mode == 2) return true;
     return n >= 4 && g.row_bytes >= 512;
 }
 
@@ -850,6 +856,13 @@ bool batch_uses_bits_path(const pir_db* db, const pir_query* qs, uint32_t n, con
 // selected it (batch_scan.cu).  d_out: n pitched answers, XOR-accumulated (zeroed here if zero_first).
 int enqueue_batch_bits(pir_db* db, const pir_query* qs, uint32_t n, const QueryGeom& g, uint8_t* d_out, cudaStream_t st,
                        bool zero_first = true) {
+    // Every key is validated and marshalled BEFORE anything is enqueued: a bad key at position k must not leave the
+    // kernels of queries 0..k-1 running on the side streams behind the caller's back.
+    std::vector<QueryConst> qcs(n);
+    for (uint32_t i = 0; i < n; i++) {
+        int rc = build_query_const(&qs[i], g.nb, &qcs[i]);
+        if (rc) return rc;
+    }
     const DeviceCtx& ctx = *db->ctx;
     const uint64_t wpq = (((g.n_rows + 31) >> 5) + 1 + 3) & ~3ull;  // +1: a slice may spill into the next word
     if ((uint64_t)n * wpq > db->bitmat_cap) {
@@ -864,7 +877,7 @@ int enqueue_batch_bits(pir_db* db, const pir_query* qs, uint32_t n, const QueryG
     // Phase-1 kernels are independent; alternating them between two streams lets the CTAs of the next
     // kernel start on SMs that the previous one has already left (each CTA fills an SM, so they never
     // share one), which hides the ramp-down of every launch.
-    const bool two_streams = n >= 2 && !getenv("PIRB_BATCH_ONE_STREAM");
+    const bool two_streams = n >= 2 && !db->tune.batch_one_stream;
     if (two_streams) {
         for (int k = 0; k < 2; k++)
             if (!db->side[k]) CU(cudaStreamCreateWithFlags(&db->side[k], cudaStreamNonBlocking));
@@ -873,25 +886,27 @@ int enqueue_batch_bits(pir_db* db, const pir_query* qs, uint32_t n, const QueryG
         CU(cudaEventRecord(db->side_ev[2], st));
         for (int k = 0; k < 2; k++) CU(cudaStreamWaitEvent(db->side[k], db->side_ev[2], 0));
     }
-    for (uint32_t i = 0; i < n; i++) {
-        QueryConst qc;
-        int rc = build_query_const(&qs[i], g.nb, &qc);
-        if (rc) return rc;
+    cudaError_t lerr = cudaSuccess;
+    for (uint32_t i = 0; i < n && lerr == cudaSuccess; i++) {
         AnswerPlan ap{};
         ap.db = db->d_slots;
         ap.row_bytes = 16;  // unused in BITS mode
         fill_answer_split(db, g, &ap, /*throughput=*/two_streams && n >= 4);
         ap.bits_out = db->d_bitmat + (uint64_t)i * wpq;
-        CU(launch_answer(qc, ap, ctx.d_t0, ctx.smem_base, ctx.num_sms, two_streams ? db->side[i & 1] : st));
+        lerr = launch_answer(qcs[i], ap, ctx.d_t0, ctx.smem_base, ctx.num_sms, two_streams ? db->side[i & 1] : st);
     }
     if (two_streams)
-        for (int k = 0; k < 2; k++) {
-            CU(cudaEventRecord(db->side_ev[k], db->side[k]));
-            CU(cudaStreamWaitEvent(st, db->side_ev[k], 0));
+        for (int k = 0; k < 2; k++) {  // join even on failure, so that `st` never runs ahead of the side streams
+            cudaError_t e1 = cudaEventRecord(db->side_ev[k], db->side[k]);
+            if (e1 == cudaSuccess) e1 = cudaStreamWaitEvent(st, db->side_ev[k], 0);
+            if (lerr == cudaSuccess) lerr = e1;
         }
+    CU(lerr);
     uint32_t tpq, segc, sr, qpl;
     batch_scan_geometry(g.row_bytes, &tpq, &segc, &sr, &qpl);
-    if (getenv("PIRB_BATCH_SKIP_SCAN")) return PIR_OK;  // timing experiments only (tools/batch_phases.py)
+#ifdef PIRB_DEV
+    if (pirb_dev::dev_skip_scan()) return PIR_OK;  // timing experiments only (tools/batch_phases.py)
+#endif
     for (uint32_t q0 = 0; q0 < n; q0 += qpl) {
         BatchScanPlan bp{};
         bp.db = db->d_slots;
@@ -918,9 +933,8 @@ int enqueue_batch_bits(pir_db* db, const pir_query* qs, uint32_t n, const QueryG
 // and the two-launch fallback share per-handle scratch and stay on one stream.
 int enqueue_batch_fused(pir_db* db, const pir_query* qs, uint32_t n, const QueryGeom& g0, uint8_t* d_out, cudaStream_t st) {
     int rc;
-    const bool v1 = getenv("PIRB_KERNEL") && !strcmp(getenv("PIRB_KERNEL"), "v1");
-    const bool two_streams = n >= 2 && !qs[0].is_keyword && !v1 && g0.n_rows != 0 && answer_kernel_supports(g0.row_bytes, 0) &&
-                             !getenv("PIRB_BATCH_ONE_STREAM") && !getenv("PIRB_PHASE_DEBUG");
+    const bool two_streams = n >= 2 && !qs[0].is_keyword && !db->tune.kernel_v1 && g0.n_rows != 0 &&
+                             answer_kernel_supports(g0.row_bytes, 0) && !db->tune.batch_one_stream && !dev_phase_debug_on();
     if (!two_streams) {
         for (uint32_t i = 0; i < n; i++)
             if ((rc = enqueue_answer(db, &qs[i], g0, d_out + (uint64_t)i * g0.row_bytes, st))) return rc;
@@ -936,7 +950,7 @@ int enqueue_batch_fused(pir_db* db, const pir_query* qs, uint32_t n, const Query
     rc = PIR_OK;
     for (uint32_t i = 0; i < n && rc == PIR_OK; i++)
         rc = enqueue_answer(db, &qs[i], g0, d_out + (uint64_t)i * g0.row_bytes, db->side[i & 1], /*zero_first=*/false, nullptr,
-                            nullptr, /*throughput=*/n >= 4 && !getenv("PIRB_BATCH_LATENCY_SPLIT"));
+                            nullptr, /*throughput=*/n >= 4 && !db->tune.batch_latency_split);
     for (int k = 0; k < 2; k++) {  // join even on failure, so that `st` never runs ahead of the side streams
         CU(cudaEventRecord(db->side_ev[k], db->side[k]));
         CU(cudaStreamWaitEvent(st, db->side_ev[k], 0));
@@ -986,10 +1000,8 @@ extern "C" int pir_answer_batch(pir_db* db, const pir_query* qs, uint32_t n_quer
     }
     // One index query answered by the warp-specialised kernel: its last CTA writes the answer straight into the pinned
     // host buffer and re-zeroes the device accumulator, so the call is one launch and one stream synchronisation.
-    static const bool no_fast = getenv("PIRB_HOST_COPY_PATH") != nullptr;  // development aid: memset + kernel + copy
-    const bool v1 = getenv("PIRB_KERNEL") && !strcmp(getenv("PIRB_KERNEL"), "v1");
-    if (n_queries == 1 && !no_fast && !v1 && db->h_out_dev && !qs[0].is_keyword && g0.n_rows != 0 &&
-        answer_kernel_supports(g0.row_bytes, 0) && !getenv("PIRB_PHASE_DEBUG")) {
+    if (n_queries == 1 && !db->tune.host_copy_path && !db->tune.kernel_v1 && db->h_out_dev && !qs[0].is_keyword &&
+        g0.n_rows != 0 && answer_kernel_supports(g0.row_bytes, 0) && !dev_phase_debug_on()) {
         if (!db->out_zeroed) CU(cudaMemsetAsync(db->d_out, 0, db->out_cap, db->stream));
         db->out_zeroed = false;
         rc = enqueue_answer(db, &qs[0], g0, db->d_out, db->stream, /*zero_first=*/false, nullptr, nullptr, false, db->h_out_dev);
@@ -1040,13 +1052,13 @@ extern "C" int pir_expand_bits(pir_db* db, const pir_query* q, uint8_t* bits_out
         if (!db->d_keywords) return fail(PIR_ERR_BAD_ARG, "keyword query on a database without keywords");
         if (geom.first_row < db->slot_begin || geom.first_row + geom.n_rows > db->slot_begin + db->slot_count)
             return fail(PIR_ERR_BAD_ARG, "keyword queries with group_size > 1 need an unsharded handle");
-        if (getenv("PIRB_KEYWORD_V1"))
+        if (db->tune.keyword_v1)
             CU(launch_eval_points(qc, db->d_keywords + (geom.first_row - db->slot_begin), 0, n_rows, nullptr,
                                   db->d_bits, ctx.d_t0, ctx.smem_base, db->stream));
         else
             CU(launch_keyword_walk(qc, db->d_keywords + (geom.first_row - db->slot_begin), 0, n_rows, nullptr,
                                    db->d_bits, ctx.d_t0, ctx.smem_base, ctx.num_sms, db->stream));
-    } else if (!getenv("PIRB_EXPAND_V1")) {
+    } else if (!db->tune.expand_v1) {
         // answer kernel in BITS mode (packed bit vector, no rows read), then one byte per row
         const uint64_t wpq = (((n_rows + 31) >> 5) + 1 + 3) & ~3ull;
         if (wpq > db->bitmat_cap) {
@@ -1065,7 +1077,7 @@ extern "C" int pir_expand_bits(pir_db* db, const pir_query* q, uint8_t* bits_out
         CU(launch_answer(qc, ap, ctx.d_t0, ctx.smem_base, ctx.num_sms, db->stream));
         CU(launch_unpack_bits(db->d_bitmat, db->d_bits, n_rows, db->stream));
     } else {
-        Plan p = make_plan(geom.nb, geom.first_row, geom.n_rows, ctx.num_sms);
+        Plan p = make_plan(geom.nb, geom.first_row, geom.n_rows, ctx.num_sms, db->tune.dfs_depth);
         if ((rc = ensure_front(db, p.task_count + 2))) return rc;
         TopPlan tp{};
         tp.Fc = p.Fc;
@@ -1124,6 +1136,36 @@ extern "C" int pir_answer_with_bits(pir_db* db, uint32_t group_size, const uint8
     return PIR_OK;
 }
 
+// Scratch of pir_dpf_eval_points, one per device, grow-only: the binding of (*Dpf).Evaluate2P (one point per
+// call in the reference, dpf/server.go:55) must not pay a cudaMalloc/cudaFree per call.
+namespace {
+struct EvalScratch {
+    std::mutex mu;
+    cudaStream_t stream = nullptr;
+    uint64_t* d_x = nullptr;
+    int64_t* d_v = nullptr;
+    uint8_t* h_pin = nullptr;  // pinned staging: n points in, n values out
+    uint64_t cap = 0;
+};
+EvalScratch g_eval[64];
+
+int eval_scratch_reserve(EvalScratch& sc, uint64_t n) {
+    if (!sc.stream) CU(cudaStreamCreateWithFlags(&sc.stream, cudaStreamNonBlocking));
+    if (n <= sc.cap) return PIR_OK;
+    uint64_t cap = sc.cap ? sc.cap : 1024;
+    while (cap < n) cap *= 2;
+    if (sc.d_x) cudaFree(sc.d_x);
+    if (sc.d_v) cudaFree(sc.d_v);
+    if (sc.h_pin) cudaFreeHost(sc.h_pin);
+    sc.d_x = nullptr, sc.d_v = nullptr, sc.h_pin = nullptr, sc.cap = 0;
+    CU(cudaMalloc(&sc.d_x, cap * 8));
+    CU(cudaMalloc(&sc.d_v, cap * 8));
+    CU(cudaMallocHost(&sc.h_pin, cap * 16));
+    sc.cap = cap;
+    return PIR_OK;
+}
+}  // namespace
+
 extern "C" int pir_dpf_eval_points(int device, const pir_query* q, const uint64_t* xs, uint64_t n, int64_t* out) {
     if (!q || (!xs && n) || (!out && n)) return fail(PIR_ERR_BAD_ARG, "null argument");
     DeviceCtx* ctx = nullptr;
@@ -1133,18 +1175,15 @@ extern "C" int pir_dpf_eval_points(int device, const pir_query* q, const uint64_
     if ((rc = build_query_const(q, q->num_bits, &qc))) return rc;
     if (n == 0) return PIR_OK;
     DeviceGuard g(device);
-    uint64_t* d_x = nullptr;
-    int64_t* d_v = nullptr;
-    CU(cudaMalloc(&d_x, n * 8));
-    cudaError_t e = cudaMalloc(&d_v, n * 8);
-    if (e == cudaSuccess) e = cudaMemcpy(d_x, xs, n * 8, cudaMemcpyHostToDevice);
-    if (e == cudaSuccess)
-        e = getenv("PIRB_KEYWORD_V1") ? launch_eval_points(qc, d_x, 0, n, d_v, nullptr, ctx->d_t0, ctx->smem_base, 0)
-                                      : launch_keyword_walk(qc, d_x, 0, n, d_v, nullptr, ctx->d_t0, ctx->smem_base, ctx->num_sms, 0);
-    if (e == cudaSuccess) e = cudaMemcpy(out, d_v, n * 8, cudaMemcpyDeviceToHost);
-    cudaFree(d_x);
-    if (d_v) cudaFree(d_v);
-    if (e != cudaSuccess) return fail(PIR_ERR_CUDA, "pir_dpf_eval_points: %s", cudaGetErrorString(e));
+    EvalScratch& sc = g_eval[device];
+    std::lock_guard<std::mutex> lk(sc.mu);
+    if ((rc = eval_scratch_reserve(sc, n))) return rc;
+    memcpy(sc.h_pin, xs, n * 8);
+    CU(cudaMemcpyAsync(sc.d_x, sc.h_pin, n * 8, cudaMemcpyHostToDevice, sc.stream));
+    CU(launch_keyword_walk(qc, sc.d_x, 0, n, sc.d_v, nullptr, ctx->d_t0, ctx->smem_base, ctx->num_sms, sc.stream));
+    CU(cudaMemcpyAsync(sc.h_pin + sc.cap * 8, sc.d_v, n * 8, cudaMemcpyDeviceToHost, sc.stream));
+    CU(cudaStreamSynchronize(sc.stream));
+    memcpy(out, sc.h_pin + sc.cap * 8, n * 8);
     return PIR_OK;
 }
 
@@ -1601,6 +1640,15 @@ extern "C" int pir_server_shard(pir_server* s, int i, pir_db** db) {
     return PIR_OK;
 }
 
+extern "C" int pir_server_set_option(pir_server* s, const char* name, int64_t value) {
+    if (!s || !name) return fail(PIR_ERR_BAD_ARG, "null argument");
+    for (pir_db* db : s->shards) {
+        int rc = pir_db_set_option(db, name, value);
+        if (rc) return rc;
+    }
+    return PIR_OK;
+}
+
 extern "C" int pir_server_upload(pir_server* s, uint64_t slot_index, const void* host_slots, uint64_t n_slots) {
     if (!s || (!host_slots && n_slots)) return fail(PIR_ERR_BAD_ARG, "null argument");
     if (slot_index > s->db_size || n_slots > s->db_size - slot_index)
@@ -1649,38 +1697,75 @@ extern "C" int pir_server_answer_batch(pir_server* s, const pir_query* qs, uint3
     if (out_len < ans * n_queries) return fail(PIR_ERR_BAD_ARG, "out_len %zu < %zu", out_len, ans * n_queries);
     int rc = server_ensure_acc(s, row_bytes * n_queries);
     if (rc) return rc;
+    // Validate every query against every shard BEFORE the first memset or launch: an error found at shard i > 0
+    // (a group size that does not divide that shard's first slot, a bad key) must not leave the kernels of the shards
+    // before it XOR-ing into the accumulator while the caller already sees a failure.
+    std::vector<QueryGeom> geoms(s->shards.size());
+    for (size_t i = 0; i < s->shards.size(); i++) {
+        for (uint32_t k = 0; k < n_queries; k++) {
+            if (qs[k].group_size != W || qs[k].is_keyword != qs[0].is_keyword)
+                return fail(PIR_ERR_BAD_ARG, "all queries of a batch must share group_size and is_keyword");
+            QueryGeom geom;
+            if ((rc = query_geom(s->shards[i], &qs[k], &geom))) return rc;
+            if (k == 0) geoms[i] = geom;
+            if (i == 0) {
+                QueryConst qc;
+                if ((rc = build_query_const(&qs[k], geom.nb, &qc))) return rc;
+            }
+        }
+        if (qs[0].is_keyword && geoms[i].n_rows && !s->shards[i]->d_keywords)
+            return fail(PIR_ERR_BAD_ARG, "keyword query on a database without keywords (pir_server_set_keywords)");
+    }
     {
         DeviceGuard g(s->owner_device);
         CU(cudaMemsetAsync(s->d_acc, 0, row_bytes * n_queries, s->stream));
         CU(cudaEventRecord(s->zeroed, s->stream));
     }
-    for (size_t i = 0; i < s->shards.size(); i++) {
+    // From here on work is in flight: a failure is remembered, the remaining shards are skipped, and the streams
+    // of the shards already started are joined before the call returns.
+    size_t started = 0;
+    for (size_t i = 0; i < s->shards.size() && rc == PIR_OK; i++) {
         pir_db* db = s->shards[i];
         std::lock_guard<std::mutex> lkdb(db->mu);
         DeviceGuard g(db->device);
-        CU(cudaStreamWaitEvent(db->stream, s->zeroed, 0));
-        QueryGeom g0;
-        if ((rc = query_geom(db, &qs[0], &g0))) return rc;
-        for (uint32_t k = 0; k < n_queries; k++) {
-            if (qs[k].group_size != W || qs[k].is_keyword != qs[0].is_keyword)
-                return fail(PIR_ERR_BAD_ARG, "all queries of a batch must share group_size and is_keyword");
-            QueryGeom geom;
-            if ((rc = query_geom(db, &qs[k], &geom))) return rc;
-        }
-        if (batch_uses_bits_path(db, qs, n_queries, g0)) {
-            // two-phase batch per shard; its scan kernel XORs into the shared accumulator like the fused one
-            if ((rc = enqueue_batch_bits(db, qs, n_queries, g0, s->d_acc, db->stream, /*zero_first=*/false))) return rc;
-        } else {
-            for (uint32_t k = 0; k < n_queries; k++)
-                if ((rc = enqueue_answer(db, &qs[k], g0, s->d_acc + (uint64_t)k * row_bytes, db->stream, false))) return rc;
-        }
-        CU(cudaEventRecord(s->done[i], db->stream));
+        auto enqueue = [&]() -> int {
+            CU(cudaStreamWaitEvent(db->stream, s->zeroed, 0));
+            int r = PIR_OK;
+            if (batch_uses_bits_path(db, qs, n_queries, geoms[i])) {
+                // two-phase batch per shard; its scan kernel XORs into the shared accumulator like the fused one
+                r = enqueue_batch_bits(db, qs, n_queries, geoms[i], s->d_acc, db->stream, /*zero_first=*/false);
+            } else {
+                for (uint32_t k = 0; k < n_queries && r == PIR_OK; k++)
+                    r = enqueue_answer(db, &qs[k], geoms[i], s->d_acc + (uint64_t)k * row_bytes, db->stream, false);
+            }
+            return r;
+        };
+        rc = enqueue();
+        started = i + 1;
+        if (cudaEventRecord(s->done[i], db->stream) != cudaSuccess && rc == PIR_OK)
+            rc = fail(PIR_ERR_CUDA, "cudaEventRecord: %s", cudaGetErrorString(cudaGetLastError()));
     }
     {
         DeviceGuard g(s->owner_device);
-        for (size_t i = 0; i < s->shards.size(); i++) CU(cudaStreamWaitEvent(s->stream, s->done[i], 0));
-        CU(cudaMemcpyAsync(s->h_acc, s->d_acc, row_bytes * n_queries, cudaMemcpyDeviceToHost, s->stream));
-        CU(cudaStreamSynchronize(s->stream));
+        for (size_t i = 0; i < started; i++) {
+            cudaError_t e = cudaStreamWaitEvent(s->stream, s->done[i], 0);
+            if (e != cudaSuccess && rc == PIR_OK) rc = fail(PIR_ERR_CUDA, "cudaStreamWaitEvent: %s", cudaGetErrorString(e));
+        }
+        if (rc == PIR_OK) {
+            cudaError_t e = cudaMemcpyAsync(s->h_acc, s->d_acc, row_bytes * n_queries, cudaMemcpyDeviceToHost, s->stream);
+            if (e != cudaSuccess) rc = fail(PIR_ERR_CUDA, "cudaMemcpyAsync: %s", cudaGetErrorString(e));
+        }
+        cudaError_t e = cudaStreamSynchronize(s->stream);
+        if (e != cudaSuccess && rc == PIR_OK) rc = fail(PIR_ERR_CUDA, "pir_server_answer_batch: %s", cudaGetErrorString(e));
+        if (rc != PIR_OK) {
+            // (if an event could not be recorded the owner stream has not waited for that shard: wait for it directly)
+            for (size_t i = 0; i < started; i++) {
+                DeviceGuard gi(s->shards[i]->device);
+                cudaStreamSynchronize(s->shards[i]->stream);
+            }
+            cudaGetLastError();
+            return rc;
+        }
     }
     for (uint32_t k = 0; k < n_queries; k++)
         for (uint32_t c = 0; c < W; c++)

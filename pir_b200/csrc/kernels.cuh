@@ -41,14 +41,16 @@ struct AnswerPlan {
     uint32_t D;           // uniform: every task has the shape (D, hi_warps): threads of the first hi_warps tree
     uint32_t hi_warps;    //   warps own 2^(D+1) rows each, the others 2^D; hi_warps = 4, 8, 12 or 16 (16 if D = 0).
     uint32_t Dmin;        // binary (hi_warps == 0): chunks of 2^(10+Dmin) rows covered by aligned tasks of depth Dmin..D
-    uint32_t pad;         // debug flags
+    uint32_t pad;         // 0 (PIRB_DEV build: experiment flags, dev_hooks.cuh)
     uint32_t slog_cap;    // log2(rows per thread per slice) at most: 3, or 2 when tasks are so shallow that the last
     uint32_t top_warp;    //   slice (whose rows are scanned after the tree warps are done) would be a large part of a CTA's work
                           // top_warp != 0: an extra warp walks the top of task k+1 during the depth-first phase of task k
     uint32_t* out;        // row_bytes/4 words, XOR-accumulated (atomics); the caller zeroes
     uint32_t* bits_out;   // BITS mode (non-null): packed selection bits, bit i = row first_row + i, OR-accumulated
                           // into a zeroed buffer of ceil(n_rows/32)+1 words; no rows are read
-    unsigned long long* dbg;  // optional per-CTA phase cycle counters (PIRB_PHASE_DEBUG), else null
+#ifdef PIRB_DEV
+    unsigned long long* dbg;  // per-CTA phase cycle counters (PIRB_PHASE_DEBUG), else null; DEV build only
+#endif
     // multi-GPU combine (optional): the last CTA to finish bumps *arrivals with system scope, after every CTA's
     // partial has been XORed into `out` (which may be peer memory); cta_done is a zeroed counter in local memory
     uint32_t* arrivals;
@@ -58,6 +60,16 @@ struct AnswerPlan {
     // Needs cta_done; not combined with `arrivals`.
     uint32_t* host_out;
 };
+
+// The in-kernel phase counters (clock64 / globaltimer) and the experiment flags exist in the PIRB_DEV build only
+// (make dev); in the shipped build these are compile-time constants and the code behind them is dropped.
+#ifdef PIRB_DEV
+#define PIRB_AP_DBG(ap) ((ap).dbg)
+#define PIRB_AP_PAD(ap) ((ap).pad)
+#else
+#define PIRB_AP_DBG(ap) (static_cast<unsigned long long*>(nullptr))
+#define PIRB_AP_PAD(ap) 0u
+#endif
 
 // Batched scan (batch_scan.cu): rows [0, n_rows) of a shard against n_queries packed bit vectors.
 struct BatchScanPlan {

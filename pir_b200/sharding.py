@@ -94,6 +94,10 @@ class Server:
         kw = np.ascontiguousarray(keywords, dtype=np.uint64)
         _capi.check(self.L.pir_server_set_keywords(self.h, kw.ctypes.data_as(C.POINTER(C.c_uint64)), kw.size))
 
+    def set_option(self, name, value):
+        """pir_server_set_option: path selection on every shard (results are bit-identical for every setting)."""
+        _capi.check(self.L.pir_server_set_option(self.h, name.encode(), int(value)))
+
     def answer(self, q):
         n = q.group_size * self.slot_bytes
         out = np.zeros(n, dtype=np.uint8)

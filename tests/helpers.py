@@ -49,6 +49,10 @@ class Handle:
     def fill(self, seed):
         _capi.check(self.L.pir_db_fill_synthetic(self.h, seed))
 
+    def set_option(self, name, value):
+        """pir_db_set_option: path selection / work-split override (results are bit-identical for every setting)."""
+        _capi.check(self.L.pir_db_set_option(self.h, name.encode(), int(value)))
+
     def set_keywords(self, kw):
         kw = np.ascontiguousarray(kw, dtype=np.uint64)
         _capi.check(self.L.pir_db_set_keywords(self.h, kw.ctypes.data_as(C.POINTER(C.c_uint64)), kw.size))

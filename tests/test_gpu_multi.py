@@ -168,15 +168,15 @@ def test_combine_over_cuda_ipc_two_gpus(gpu_lib):
     assert q.get(timeout=5) is True
 
 
-def test_server_batch_two_phase_over_shards(gpu_lib, monkeypatch):
+def test_server_batch_two_phase_over_shards(gpu_lib):
     """pir_server_answer_batch with wide rows: every shard runs the bit-vector + single-pass scan path and
     XORs into the shared accumulator."""
     db_size, S, nq = 1 << 13, 1024, 6
     data = oracle.synth_fill(8, 0, db_size, S)
     pairs = [make_queries(50 + i, db_size, 1, (i * 1237) % db_size) for i in range(nq)]
     qs = [p[1][0] for p in pairs]
-    monkeypatch.setenv("PIRB_BATCH_MODE", "bits")
     with sharding.Server(_devices(gpu_lib, 3), db_size, S) as srv:
+        srv.set_option("batch_mode", 2)
         srv.fill_synthetic(8)
         got = srv.answer_batch(qs)
     for i, p in enumerate(pairs):

@@ -213,7 +213,7 @@ def test_error_paths(gpu_lib, capi):
     (1 << 14, 1024, 1, 6, 5000, 7000),     # a shard whose first row is not a multiple of 32
     (777, 16, 1, 8, 0, None),              # tiny rows
 ])
-def test_batch_two_phase_path_matches_oracle(gpu_lib, monkeypatch, db_size, slot_bytes, W, nq, first, count):
+def test_batch_two_phase_path_matches_oracle(gpu_lib, db_size, slot_bytes, W, nq, first, count):
     """pir_answer_batch through the bit-vector + single-pass scan path (answer_kernel BITS mode +
     batch_scan_kernel) equals the oracle answer of every query, and equals the fused path."""
     data = oracle.synth_fill(21, 0, db_size, slot_bytes)
@@ -225,9 +225,9 @@ def test_batch_two_phase_path_matches_oracle(gpu_lib, monkeypatch, db_size, slot
     os_ = [p[0][i & 1] for i, p in enumerate(pairs)]
     with Handle(db_size, slot_bytes, slot_begin=first * W, slot_count=None if count is None else count * W) as h:
         h.fill(21)
-        monkeypatch.setenv("PIRB_BATCH_MODE", "bits")
+        h.set_option("batch_mode", 2)   # bit vectors + one scan pass
         got = h.answer_batch(qs)
-        monkeypatch.setenv("PIRB_BATCH_MODE", "fused")
+        h.set_option("batch_mode", 1)   # one fused launch per query
         fused = h.answer_batch(qs)
     assert np.array_equal(got, fused)
     if count is None:
@@ -236,13 +236,12 @@ def test_batch_two_phase_path_matches_oracle(gpu_lib, monkeypatch, db_size, slot
 
 
 @pytest.mark.parametrize("db_size,slot_bytes,W,nq", [
-    # Was an intermittent mismatch: pir_db_create zeroed the padding of 100-byte slots with a
-    # cudaMemset() on the legacy stream that a fill on the handle's non-blocking stream could overtake.  Fixed
-    # (stream-ordered memset); the fix could not be confirmed over enough process starts in the round it was made, so the
-    # case stays a non-strict xfail until it has been (tools/flaky_loop.sh, tools/flaky_bits_probe.py).
-    pytest.param(3000, 100, 3, 4, marks=pytest.mark.xfail(strict=False, reason="was intermittent; fix to be confirmed, DESIGN.md 7")),
-    (5000, 512, 1, 5), (1 << 15, 256, 1, 6)])
-def test_batch_paths_are_repeatable(gpu_lib, monkeypatch, db_size, slot_bytes, W, nq):
+    # (3000, 100, 3, 4) was an intermittent mismatch in round 1: pir_db_create zeroed the padding
+    # of 100-byte slots with a cudaMemset() on the legacy stream that a fill on the handle's non-blocking stream could
+    # overtake.  Fixed (stream-ordered memset, waited for) and confirmed over several hundred process starts
+    # (tools/flaky_loop.sh, profiles/r2_flaky_loop.txt); a wrong answer here fails the suite.
+    (3000, 100, 3, 4), (5000, 512, 1, 5), (1 << 15, 256, 1, 6)])
+def test_batch_paths_are_repeatable(gpu_lib, db_size, slot_bytes, W, nq):
     """The batch paths run kernels on two side streams against per-handle scratch: the same batch, answered 40
     times by fresh handles through both paths, must give the oracle's bytes every time (a race would not)."""
     data = oracle.synth_fill(21, 0, db_size, slot_bytes)
@@ -255,24 +254,24 @@ def test_batch_paths_are_repeatable(gpu_lib, monkeypatch, db_size, slot_bytes, W
         with Handle(db_size, slot_bytes) as h:
             h.fill(21)
             for mode in ("bits", "fused"):
-                monkeypatch.setenv("PIRB_BATCH_MODE", mode)
+                h.set_option("batch_mode", 2 if mode == "bits" else 1)
                 got = np.asarray(h.answer_batch(qs)).reshape(nq, -1)
                 assert np.array_equal(got, want), (rep, mode)
 
 
 @pytest.mark.parametrize("top_warp", ["1", "0"])
 @pytest.mark.parametrize("split", [("1", "0"), ("2", "1")])
-def test_several_tasks_per_cta_with_and_without_top_walker(gpu_lib, monkeypatch, top_warp, split):
-    """A shard cut into several tasks per CTA (binary split forced through the development switches): the tops of the
+def test_several_tasks_per_cta_with_and_without_top_walker(gpu_lib, top_warp, split):
+    """A shard cut into several tasks per CTA (binary split forced through pir_db_set_option): the tops of the
     tasks ahead are walked by the last scan warp (TopWalker, answer_kernel.cu) or by the tree warps themselves; both
     must give the oracle's bytes for both shares.  (The shipped splits of the small test databases are one task per
     CTA, so without this test the walker would only run on databases of 2^26 rows and more.)"""
     db_size, slot_bytes = 1 << 19, 128
-    monkeypatch.setenv("PIRB_DFS_DEPTH", split[0])
-    monkeypatch.setenv("PIRB_DMIN", split[1])
-    monkeypatch.setenv("PIRB_TOP_WARP", top_warp)
     data = oracle.synth_fill(33, 0, db_size, slot_bytes)
     with Handle(db_size, slot_bytes) as h:
+        h.set_option("dfs_depth", split[0])
+        h.set_option("dmin", split[1])
+        h.set_option("top_warp", top_warp)
         h.fill(33)
         for k, idx in enumerate((0, 123457, db_size - 1)):
             os_, qs = make_queries(40 + k, db_size, 1, idx)
@@ -285,7 +284,7 @@ def test_several_tasks_per_cta_with_and_without_top_walker(gpu_lib, monkeypatch,
 
 
 @pytest.mark.parametrize("kind", ["dense_sorted", "duplicates", "unsorted", "clustered", "wide64"])
-def test_keyword_prefix_sharing_kernel_matches_oracle(gpu_lib, monkeypatch, kind):
+def test_keyword_prefix_sharing_kernel_matches_oracle(gpu_lib, kind):
     """The keyword path restarts each row's walk below the last node it shares with the previous row
     (keyword_kernel.cu).  Bits must equal the oracle's per-row 32-level Evaluate2P (db.go:132-147) for any
     keyword order, with repeated keywords, and equal the plain per-row kernel."""
@@ -307,10 +306,9 @@ def test_keyword_prefix_sharing_kernel_matches_oracle(gpu_lib, monkeypatch, kind
     with Handle(db_size, slot_bytes) as h:
         h.fill(3)
         h.set_keywords(kws)
-        monkeypatch.delenv("PIRB_KEYWORD_V1", raising=False)
         b0, b1 = h.expand_bits(q0), h.expand_bits(q1)
         a0, a1 = h.answer(q0), h.answer(q1)
-        monkeypatch.setenv("PIRB_KEYWORD_V1", "1")
+        h.set_option("keyword_v1", 1)   # the plain per-row 32-level walk
         assert np.array_equal(h.expand_bits(q0), b0)
     assert np.array_equal(b0, oracle.expand_shared_query(o0, db_size, keywords=kws))
     assert np.array_equal(b1, oracle.expand_shared_query(o1, db_size, keywords=kws))
