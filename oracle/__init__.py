@@ -14,6 +14,7 @@ from .loader import (  # noqa: F401
     expand_tree,
     answer_with_bits,
     answer,
+    answers_over_synth,
     synth_fill,
     tape,
     num_bits_for,

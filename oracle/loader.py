@@ -89,6 +89,7 @@ def lib():
     L.orc_synth_fill.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, u8p]
     L.orc_synth_word.argtypes = [C.c_uint64, C.c_uint64, C.c_uint32]
     L.orc_synth_word.restype = C.c_uint64
+    L.orc_answers_over_synth.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint64, u8p, C.c_uint32, u8p, C.c_int]
     L.orc_tape.argtypes = [C.c_uint64, u8p, C.c_size_t]
     if L.orc_aes_selftest() != 0:
         raise RuntimeError("oracle AES self-test failed (FIPS-197 vectors)")
@@ -177,6 +178,17 @@ def answer(q, slots, db_size, slot_bytes, keywords=None, nthreads=1, use_tree=Fa
         kw = np.ascontiguousarray(keywords, dtype=np.uint64)
     lib().orc_answer(C.byref(q), _u8(slots), db_size, slot_bytes, _u64(kw) if kw is not None else None,
                      _u8(out), nthreads, int(use_tree))
+    return out
+
+
+def answers_over_synth(seed, slot_bytes, group_size, bits_list, row_begin=0, nthreads=1):
+    """db.go:75-107 for several bit vectors at once over the synthetic database `seed` (rows generated on the fly,
+    nothing of the 4-8 GiB database is kept on the host).  bits_list: equal-length uint8 vectors for rows
+    [row_begin, row_begin + len).  Returns one answer (group_size*slot_bytes bytes) per vector."""
+    bits = np.ascontiguousarray(np.stack([np.asarray(b, dtype=np.uint8) for b in bits_list]))
+    nq, n_rows = bits.shape
+    out = np.zeros((nq, group_size * slot_bytes), dtype=np.uint8)
+    lib().orc_answers_over_synth(seed, slot_bytes, group_size, row_begin, n_rows, _u8(bits), nq, _u8(out), nthreads)
     return out
 
 

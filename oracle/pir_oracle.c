@@ -296,6 +296,78 @@ void orc_synth_fill(uint64_t seed, uint64_t slot_begin, uint64_t n_slots, uint32
     }
 }
 
+/* ---- answers over the synthetic database without materialising it ------------------------------ */
+/* PrivateSecretSharedQueryWithExpandedBits (db.go:75-107) for nq bit vectors at once over the database that
+ * orc_synth_fill(seed) defines: every row of rows [row_begin, row_begin + n_rows) is generated on the fly and
+ * XORed (slot.go:19-30) into the answer of every query whose bit for it is set.  bits is [nq][n_rows], out is
+ * [nq][group_size*slot_bytes] (zeroed here).  Rows are split statically over nthreads.  This is what lets a
+ * test or bench.py check a full-size (4-8 GiB) GPU answer against the restated algorithm on the host. */
+typedef struct synth_job {
+    uint64_t seed, row_begin, n_rows, stride;
+    uint32_t slot_bytes, group_size, nq;
+    const uint8_t* bits;
+    uint8_t* acc; /* [nq][row_bytes], private to the thread */
+} synth_job;
+
+static void* synth_answer_worker(void* p) {
+    synth_job* j = (synth_job*)p;
+    const size_t row_bytes = (size_t)j->group_size * j->slot_bytes;
+    uint8_t* row = (uint8_t*)malloc(row_bytes + 8);
+    for (uint64_t r = 0; r < j->n_rows; r++) {
+        int any = 0;
+        for (uint32_t q = 0; q < j->nq && !any; q++) any = j->bits[(size_t)q * j->stride + r] != 0;
+        if (!any) continue; /* db.go:93 */
+        const uint64_t slot0 = (j->row_begin + r) * j->group_size;
+        if ((j->slot_bytes & 7u) == 0) { /* whole words: the same bytes as orc_synth_fill, eight at a time */
+            uint64_t* w = (uint64_t*)row;
+            const uint32_t wps = j->slot_bytes / 8;
+            for (uint32_t c = 0; c < j->group_size; c++)
+                for (uint32_t k = 0; k < wps; k++) w[(size_t)c * wps + k] = orc_synth_word(j->seed, slot0 + c, k);
+        } else {
+            orc_synth_fill(j->seed, slot0, j->group_size, j->slot_bytes, row);
+        }
+        for (uint32_t q = 0; q < j->nq; q++) {
+            if (!j->bits[(size_t)q * j->stride + r]) continue;
+            uint8_t* a = j->acc + (size_t)q * row_bytes;
+            size_t k = 0;
+            for (; k + 8 <= row_bytes; k += 8) { /* XorSlots, eight bytes at a time */
+                uint64_t x, y;
+                memcpy(&x, a + k, 8);
+                memcpy(&y, row + k, 8);
+                x ^= y;
+                memcpy(a + k, &x, 8);
+            }
+            for (; k < row_bytes; k++) a[k] ^= row[k];
+        }
+    }
+    free(row);
+    return NULL;
+}
+
+void orc_answers_over_synth(uint64_t seed, uint32_t slot_bytes, uint32_t group_size, uint64_t row_begin,
+                            uint64_t n_rows, const uint8_t* bits, uint32_t nq, uint8_t* out, int nthreads) {
+    const size_t row_bytes = (size_t)group_size * slot_bytes;
+    memset(out, 0, (size_t)nq * row_bytes);
+    if (nthreads < 1) nthreads = 1;
+    if ((uint64_t)nthreads > n_rows) nthreads = n_rows ? (int)n_rows : 1;
+    pthread_t* th = (pthread_t*)malloc(sizeof(pthread_t) * (size_t)nthreads);
+    synth_job* jobs = (synth_job*)malloc(sizeof(synth_job) * (size_t)nthreads);
+    for (int t = 0; t < nthreads; t++) {
+        const uint64_t b = n_rows * (uint64_t)t / (uint64_t)nthreads, e = n_rows * (uint64_t)(t + 1) / (uint64_t)nthreads;
+        synth_job j = {seed, row_begin + b, e - b, n_rows, slot_bytes, group_size, nq, bits + b,
+                       (uint8_t*)calloc((size_t)nq ? (size_t)nq : 1, row_bytes)};
+        jobs[t] = j;
+        pthread_create(&th[t], NULL, synth_answer_worker, &jobs[t]);
+    }
+    for (int t = 0; t < nthreads; t++) {
+        pthread_join(th[t], NULL);
+        for (size_t k = 0; k < (size_t)nq * row_bytes; k++) out[k] ^= jobs[t].acc[k];
+        free(jobs[t].acc);
+    }
+    free(th);
+    free(jobs);
+}
+
 void orc_tape(uint64_t seed, uint8_t* out, size_t n) {
     uint64_t x = seed;
     for (size_t i = 0; i < n; i++) {

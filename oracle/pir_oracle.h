@@ -61,6 +61,10 @@ void orc_answer(const pir_query* q, const uint8_t* slots, uint64_t db_size, uint
 void orc_synth_fill(uint64_t seed, uint64_t slot_begin, uint64_t n_slots, uint32_t slot_bytes,
                     uint8_t* out);
 uint64_t orc_synth_word(uint64_t seed, uint64_t slot, uint32_t w);
+/* db.go:75-107 for nq bit vectors ([nq][n_rows] bytes) over rows [row_begin, +n_rows) of the synthetic database,
+ * generated on the fly (no 4-8 GiB host copy); out = [nq][group_size*slot_bytes]. */
+void orc_answers_over_synth(uint64_t seed, uint32_t slot_bytes, uint32_t group_size, uint64_t row_begin,
+                            uint64_t n_rows, const uint8_t* bits, uint32_t nq, uint8_t* out, int nthreads);
 /* deterministic byte tape for key generation in tests (splitmix64 stream) */
 void orc_tape(uint64_t seed, uint8_t* out, size_t n);
 

@@ -51,7 +51,7 @@ constexpr uint32_t kMaxTasks = 512;            // per CTA (launch_answer sizes t
 constexpr uint32_t kOffPathS = kV2MaxDepth * 4 * kTreeThreads * 4;  // [65] uint4: the single-node levels above a task
 constexpr uint32_t kOffPathT = kOffPathS + 65 * 16;                 // [65] u8 (+ pad)
 constexpr uint32_t kOffTasks = kOffPathT + 80;                      // task list: header (n, base, stride) + [kMaxTasks] u32
-constexpr uint32_t kTaskHeader = 6;                                 // u32 words before the entries
+constexpr uint32_t kTaskHeader = 8;                                 // u32 words before the entries
 constexpr uint32_t kOffTopScrS = (kOffTasks + 4 * (kTaskHeader + kMaxTasks) + 15u) & ~15u;  // top warp: [kHand] uint4 level buffer
 constexpr uint32_t kOffTopScrT = kOffTopScrS + kHand * 16;          // [kHand] u8
 constexpr uint32_t kOffPath2S = kOffTopScrT + kHand;                // top warp: [65] uint4 single-node levels
@@ -230,8 +230,15 @@ __device__ __forceinline__ void fold_acc(const ScanLane& sl, uint4 (&accs)[NCB])
 
 constexpr uint32_t kGroups = kTreeThreads / 32;  // 32-word groups per slice
 
-__host__ __device__ __forceinline__ uint64_t answer_tasks_of(uint64_t first_row, uint64_t n_rows, uint32_t D, uint32_t hi_warps) {
-    const uint64_t R = (uint64_t)(16u + hi_warps) << (D + 5u);
+// level-L nodes (2^(D+1) rows each) a uniform task spans: the shape's own 32*hiw + 16*(16 - hiw), or fewer when the
+// host trims the tasks so that they fill every SM equally (AnswerPlan::m_task; the trailing threads then idle)
+__host__ __device__ __forceinline__ uint32_t task_nodes(uint32_t hi_warps, uint32_t m_task) {
+    const uint32_t nom = 32u * hi_warps + 16u * (16u - hi_warps);
+    return (m_task != 0u && m_task < nom) ? m_task : nom;
+}
+__host__ __device__ __forceinline__ uint64_t answer_tasks_of(uint64_t first_row, uint64_t n_rows, uint32_t D, uint32_t hi_warps,
+                                                             uint32_t m_task) {
+    const uint64_t R = (uint64_t)task_nodes(hi_warps, m_task) << (D + 1u);
     const uint64_t T0 = first_row & ~((2ull << D) - 1ull);
     return (first_row + n_rows - T0 + R - 1ull) / R;
 }
@@ -260,14 +267,14 @@ struct TaskShape {
     uint32_t m_hi, m_nom;  // hi thread roots; nodes of the hi roots' tree level the task spans (hi roots + lo parents)
     uint32_t slog, n_slices_log;
     uint64_t R;
-    __device__ __forceinline__ void set(uint32_t d, uint32_t hi_warps, uint32_t slog_cap) {
+    __device__ __forceinline__ void set(uint32_t d, uint32_t hi_warps, uint32_t slog_cap, uint32_t m_task) {
         D = d;
         hiw = hi_warps;
         m_hi = 32u * hiw;
-        m_nom = m_hi + 16u * (kTreeWarps - hiw);
+        m_nom = task_nodes(hiw, m_task);
         slog = slice_log(D, slog_cap);
         n_slices_log = D + 1u - slog;
-        R = (uint64_t)(kTreeWarps + hiw) << (D + 5u);
+        R = (uint64_t)m_nom << (D + 1u);
     }
     // first row, log2(rows per thread) and log2(rows per thread per slice) of tree warp g's threads
     __device__ __forceinline__ void group_geom(uint32_t g, uint64_t row0, uint64_t& grow0, uint32_t& rows_log, uint32_t& gslog) const {
@@ -301,7 +308,7 @@ struct ChunkRange {
     }
 };
 
-// The CTA's task list in shared memory: n, the slice cap (log2), then (64-bit) base and stride, then n entries
+// The CTA's task list in shared memory: n, the slice cap (log2), then (64-bit) base and stride, m_task, then n entries
 // (offset << 5 | (hi_warps/4 - 1) << 3 | d); a task's first row is base + offset * stride.
 struct TaskIter {
     const uint32_t* list;
@@ -310,7 +317,7 @@ struct TaskIter {
     __device__ __forceinline__ void decode(uint32_t k, uint64_t& row_start, TaskShape& ts) const {
         const uint32_t e = list[kTaskHeader + k];
         const uint64_t base = *reinterpret_cast<const uint64_t*>(list + 2), stride = *reinterpret_cast<const uint64_t*>(list + 4);
-        ts.set(e & 7u, 4u * (((e >> 3) & 3u) + 1u), list[1]);
+        ts.set(e & 7u, 4u * (((e >> 3) & 3u) + 1u), list[1], list[6]);
         row_start = base + (uint64_t)(e >> 5) * stride;
     }
     __device__ __forceinline__ uint32_t slices_log(uint32_t k) const {  // log2(slices of task k)
@@ -325,10 +332,10 @@ __device__ __forceinline__ void build_task_list(const AnswerPlan& ap, uint32_t* 
     uint32_t* entries = task_list + kTaskHeader;
     if (ap.hi_warps) {
         TaskShape ts;
-        ts.set(ap.D, ap.hi_warps, ap.slog_cap);
+        ts.set(ap.D, ap.hi_warps, ap.slog_cap, ap.m_task);
         base = (ap.first_row & ~((2ull << ap.D) - 1ull)) + (uint64_t)blockIdx.x * ts.R;
         stride = (uint64_t)gridDim.x * ts.R;
-        const uint64_t NT = answer_tasks_of(ap.first_row, ap.n_rows, ap.D, ap.hi_warps);
+        const uint64_t NT = answer_tasks_of(ap.first_row, ap.n_rows, ap.D, ap.hi_warps, ap.m_task);
         if (blockIdx.x < NT) n = (uint32_t)((NT - blockIdx.x + gridDim.x - 1ull) / gridDim.x);
         if (n > kMaxTasks) __trap();  // launch_answer sizes the grid so that this cannot happen
         for (uint32_t k = 0; k < n; k++) entries[k] = (k << 5) | ((ap.hi_warps / 4u - 1u) << 3) | ap.D;
@@ -355,6 +362,7 @@ __device__ __forceinline__ void build_task_list(const AnswerPlan& ap, uint32_t* 
     }
     task_list[0] = n;
     task_list[1] = ap.slog_cap;
+    task_list[6] = ap.hi_warps ? ap.m_task : 0u;
     *reinterpret_cast<uint64_t*>(task_list + 2) = base;
     *reinterpret_cast<uint64_t*>(task_list + 4) = stride;
 }
@@ -949,6 +957,12 @@ __global__ void __launch_bounds__(kAnswerThreads, 1)
 answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ AnswerPlan ap,
               const uint32_t* __restrict__ t0) {
     const uint32_t base = smem_addr(g_smem2);
+    // Programmatic dependent launch: the next answer kernel in the stream may start its CTAs on SMs this launch has
+    // already left (table fill, tree top and expansion read only the database and the key).  Everything a launch
+    // WRITES to global memory comes after griddepcontrol.wait, i.e. after the launch before it has completed, so
+    // the accumulators and counters are used strictly in stream order.
+    asm volatile("griddepcontrol.launch_dependents;");
+    if constexpr (NCB == 0) asm volatile("griddepcontrol.wait;" ::: "memory");  // (BITS mode writes as it goes)
     const long long c_entry = PIRB_AP_DBG(ap) ? clock64() : 0;
     if (PIRB_AP_DBG(ap) && threadIdx.x == 0) {  // CTA start on the GPU-wide timer (ns): launch stagger across SMs
         unsigned long long gt;
@@ -992,14 +1006,16 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
     }
     if constexpr (NCB != 0) {  // (BITS mode has nothing to fold)
         __syncthreads();
+        asm volatile("griddepcontrol.wait;" ::: "memory");
         for (uint32_t i = threadIdx.x; i < words_out; i += kAnswerThreads) {
             const uint32_t v = red[i];
             if (v) atomicXor(&ap.out[i], v);
         }
-        if (ap.host_out) {
-            // Host call on one GPU: every CTA's XORs are fenced and counted; the last CTA reads the finished words
+        if (ap.final_out) {
+            // Single-GPU call: every CTA's XORs are fenced and counted; the last CTA reads the finished words
             // (atomicExch: the read also re-zeroes the accumulator for the next query) and stores them to the
-            // caller's mapped pinned buffer, visible to the host once the kernel has completed.
+            // caller's buffer -- device memory, or a mapped pinned host buffer that the host sees once the kernel
+            // has completed.  One launch per query: no memset before and no copy after the kernel.
             __threadfence();
             __syncthreads();
             uint32_t* flag = reinterpret_cast<uint32_t*>(g_smem2 + (kAbsClaim - smem_addr(g_smem2)));  // (free by now)
@@ -1011,7 +1027,7 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
             __syncthreads();
             if (*flag) {
                 __threadfence();
-                for (uint32_t i = threadIdx.x; i < words_out; i += kAnswerThreads) ap.host_out[i] = atomicExch(&ap.out[i], 0u);
+                for (uint32_t i = threadIdx.x; i < words_out; i += kAnswerThreads) ap.final_out[i] = atomicExch(&ap.out[i], 0u);
                 __threadfence_system();
             }
         } else if (ap.arrivals) {
@@ -1060,16 +1076,17 @@ cudaError_t configure_answer_kernel() {
     return e;
 }
 
-uint64_t answer_tasks(uint64_t first_row, uint64_t n_rows, uint32_t D, uint32_t hi_warps) {
-    return answer_tasks_of(first_row, n_rows, D, hi_warps);
+uint64_t answer_tasks(uint64_t first_row, uint64_t n_rows, uint32_t D, uint32_t hi_warps, uint32_t m_task) {
+    return answer_tasks_of(first_row, n_rows, D, hi_warps, m_task);
 }
+uint32_t answer_task_nodes(uint32_t hi_warps, uint32_t m_task) { return task_nodes(hi_warps, m_task); }
 uint64_t answer_chunks(uint64_t first_row, uint64_t n_rows, uint32_t Dmin) {
     const uint32_t cl = 10u + Dmin;
     return ((first_row + n_rows + ((1ull << cl) - 1ull)) >> cl) - (first_row >> cl);
 }
 
 cudaError_t launch_answer(const QueryConst& qc, const AnswerPlan& ap, const uint32_t* d_t0, uint32_t smem_base,
-                          int num_sms, cudaStream_t st) {
+                          int num_sms, cudaStream_t st, bool overlap) {
     if (ap.n_rows == 0) return cudaSuccess;
     if (ap.D > (uint32_t)kV2MaxDepth || ap.D + 1u > qc.num_bits || ap.hi_warps > (uint32_t)kTreeWarps || (ap.hi_warps & 3u) ||
         (ap.hi_warps != 0u && ap.hi_warps < (uint32_t)kTreeWarps && ap.D == 0u) || (ap.hi_warps == 0u && ap.Dmin > ap.D) ||
@@ -1077,7 +1094,7 @@ cudaError_t launch_answer(const QueryConst& qc, const AnswerPlan& ap, const uint
         return cudaErrorInvalidValue;
     // units the CTAs share out: tasks (uniform split) or chunks (binary split).  A CTA's task list holds
     // kMaxTasks entries: very large shards run more CTAs than SMs (in waves) rather than overflow it.
-    const uint64_t units = ap.hi_warps ? answer_tasks(ap.first_row, ap.n_rows, ap.D, ap.hi_warps)
+    const uint64_t units = ap.hi_warps ? answer_tasks(ap.first_row, ap.n_rows, ap.D, ap.hi_warps, ap.m_task)
                                        : answer_chunks(ap.first_row, ap.n_rows, ap.Dmin);
     uint64_t g = units < (uint64_t)num_sms ? units : (uint64_t)num_sms;
     const uint64_t gmin = (units + (kMaxTasks - 1)) / kMaxTasks;
@@ -1086,12 +1103,23 @@ cudaError_t launch_answer(const QueryConst& qc, const AnswerPlan& ap, const uint
     // two code paths per row geometry: keys with an odd FinalCW need the leaves' control bits, keys with an
     // even one do not (aes_unrolled.cuh, leaf_parent_tail_even)
     const bool odd = qc.fcw_parity != 0 || (PIRB_AP_PAD(ap) & 2u);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)g);
+    cfg.blockDim = dim3(kAnswerThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = overlap ? 1 : 0;
+    cudaError_t lerr = cudaSuccess;
 #define PIRB_LAUNCH(NCB)                                                                           \
     do {                                                                                           \
         if (odd)                                                                                   \
-            answer_kernel<NCB, true><<<(unsigned)g, kAnswerThreads, smem, st>>>(qc, ap, d_t0);     \
+            lerr = cudaLaunchKernelEx(&cfg, answer_kernel<NCB, true>, qc, ap, d_t0);               \
         else                                                                                       \
-            answer_kernel<NCB, false><<<(unsigned)g, kAnswerThreads, smem, st>>>(qc, ap, d_t0);    \
+            lerr = cudaLaunchKernelEx(&cfg, answer_kernel<NCB, false>, qc, ap, d_t0);              \
     } while (0)
     if (ap.bits_out)
         PIRB_LAUNCH(0);
@@ -1105,7 +1133,7 @@ cudaError_t launch_answer(const QueryConst& qc, const AnswerPlan& ap, const uint
         PIRB_LAUNCH(8);
 #undef PIRB_LAUNCH
     count_launch();
-    return cudaGetLastError();
+    return lerr != cudaSuccess ? lerr : cudaGetLastError();
 }
 
 }  // namespace pirb

@@ -227,6 +227,9 @@ struct Tuning {
     bool serial_launch = false;   // no programmatic dependent launch between consecutive answer kernels
 };
 
+constexpr uint32_t kCtaDoneRing = 64;
+constexpr size_t kAnswerMaxRowBytes = 4096;  // widest row the warp-specialised kernel takes (answer_kernel_supports)
+
 struct pir_db {
     int device = 0;
     DeviceCtx* ctx = nullptr;
@@ -255,7 +258,13 @@ struct pir_db {
     uint64_t out_cap = 0;
     uint8_t* h_out = nullptr;  // pinned
     uint32_t* h_out_dev = nullptr;  // the same buffer as the device sees it (cudaHostGetDevicePointer)
-    bool out_zeroed = false;        // d_out holds zeros: the answer kernel's last CTA left it so (AnswerPlan::host_out)
+    // One-launch single queries (AnswerPlan::final_out): every CTA XORs into this 4 KB accumulator and the launch's last
+    // CTA moves the finished answer to its destination and leaves the accumulator zeroed.  It is all zeros between
+    // launches; launches that use it are ordered by the stream (their global writes wait for the launch before,
+    // answer_kernel.cu griddepcontrol.wait), and a call on another stream first waits for the last user (acc_ev).
+    uint8_t* d_acc = nullptr;
+    cudaStream_t acc_stream = nullptr;
+    cudaEvent_t acc_ev = nullptr;
     uint64_t h_out_cap = 0;
     // cached work split of the answer kernel for the last (num_bits, shard rows) seen
     uint32_t split_nb = 0, split_d = 0, split_hiw = 0, split_dmin = 0;
@@ -301,7 +310,6 @@ int ensure_out(pir_db* db, uint64_t n) {
         db->out_cap = 0;
         CU(cudaMalloc(&db->d_out, n));
         db->out_cap = n;
-        db->out_zeroed = false;
     }
     if (n > db->h_out_cap) {
         if (db->h_out) cudaFreeHost(db->h_out);
@@ -484,6 +492,11 @@ extern "C" int pir_db_create(int device, uint64_t db_size, uint32_t slot_bytes, 
     // Every slot starts as zeros, like the reference's make([]byte, n) (slot.go:137-170): a query on a handle that has
     // been uploaded only in part must not XOR stale device memory into the answer.
     if (e == cudaSuccess) e = cudaMemsetAsync(db->d_slots, 0, bytes ? bytes : 16, db->stream);
+    if (e == cudaSuccess) e = cudaMalloc(&db->d_acc, kAnswerMaxRowBytes);
+    if (e == cudaSuccess) e = cudaMemsetAsync(db->d_acc, 0, kAnswerMaxRowBytes, db->stream);
+    if (e == cudaSuccess) e = cudaMalloc(&db->d_cta_done, kCtaDoneRing * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMemsetAsync(db->d_cta_done, 0, kCtaDoneRing * sizeof(uint32_t), db->stream);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&db->acc_ev, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaStreamSynchronize(db->stream);
     if (e != cudaSuccess) {
         int code = e == cudaErrorMemoryAllocation ? PIR_ERR_OOM : PIR_ERR_CUDA;
@@ -507,6 +520,8 @@ extern "C" int pir_db_destroy(pir_db* db) {
     if (db->d_bits) cudaFree(db->d_bits);
     if (db->d_bitmat) cudaFree(db->d_bitmat);
     if (db->d_cta_done) cudaFree(db->d_cta_done);
+    if (db->d_acc) cudaFree(db->d_acc);
+    if (db->acc_ev) cudaEventDestroy(db->acc_ev);
     for (int k = 0; k < 2; k++)
         if (db->side[k]) cudaStreamDestroy(db->side[k]);
     for (int k = 0; k < 3; k++)
@@ -687,14 +702,13 @@ int query_geom(const pir_db* db, const pir_query* q, QueryGeom* g) {
 }
 
 // Enqueue one query's work on `st`; d_out receives the pitched answer (row_bytes bytes).
-constexpr uint32_t kCtaDoneRing = 64;
 
 // arrivals / signalled: multi-GPU combine.  When the warp-specialised kernel answers the query, its last CTA
 // bumps *arrivals itself (system scope, after its partial has been XORed into d_out) and *signalled is set;
 // on every other path the caller launches the signalling kernel.
 int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* d_out, cudaStream_t st,
                    bool zero_first = true, uint32_t* arrivals = nullptr, bool* signalled = nullptr, bool throughput = false,
-                   uint32_t* host_out = nullptr) {
+                   uint32_t* final_out = nullptr) {
     // every kernel below XOR-accumulates into d_out (atomics), so a caller that combines several shards
     // into one buffer passes zero_first = false and zeroes it once itself
     if (zero_first) CU(cudaMemsetAsync(d_out, 0, g.row_bytes, st));
@@ -724,14 +738,18 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
         ap.row_bytes = g.row_bytes;
         fill_answer_split(db, g, &ap, throughput);
         ap.out = (uint32_t*)d_out;
-        if (((arrivals && signalled) || host_out) && !db->d_cta_done) {
-            CU(cudaMalloc(&db->d_cta_done, kCtaDoneRing * sizeof(uint32_t)));
-            // (stream-ordered and waited for: a cudaMemset() on the legacy stream could overtake the kernels' counting)
-            CU(cudaMemsetAsync(db->d_cta_done, 0, kCtaDoneRing * sizeof(uint32_t), st));
-            CU(cudaStreamSynchronize(st));
-        }
-        if (host_out) {  // (the caller has checked that this branch will be taken: host_fast_path)
-            ap.host_out = host_out;
+        if (final_out) {  // (the caller has checked that this branch will be taken: single_launch_ok; d_out is db->d_acc)
+            if (db->acc_stream && db->acc_stream != st) {
+                // the accumulator's last user ran on another stream: this launch must not overlap it
+                cudaError_t e = cudaEventRecord(db->acc_ev, db->acc_stream);
+                if (e == cudaSuccess) e = cudaStreamWaitEvent(st, db->acc_ev, 0);
+                if (e != cudaSuccess) {  // (e.g. the caller has destroyed that stream since)
+                    cudaGetLastError();
+                    CU(cudaDeviceSynchronize());
+                }
+            }
+            db->acc_stream = st;
+            ap.final_out = final_out;
             ap.cta_done = db->d_cta_done + (db->cta_done_next++ % kCtaDoneRing);
         } else if (arrivals && signalled && !db->tune.signal_kernel) {
             ap.arrivals = arrivals;
@@ -754,7 +772,8 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
             db->ev_used++;
             CU(cudaEventRecord(e0, st));
         }
-        CU(launch_answer(qc, ap, ctx.d_t0, ctx.smem_base, ctx.num_sms, st));
+        // consecutive answer launches overlap (programmatic dependent launch) unless a launch is being timed on its own
+        CU(launch_answer(qc, ap, ctx.d_t0, ctx.smem_base, ctx.num_sms, st, /*overlap=*/!db->timing && !db->tune.serial_launch));
         if (e1) CU(cudaEventRecord(e1, st));
 #ifdef PIRB_DEV
         if (int drc = dev_phase.report(st)) return drc;
@@ -828,6 +847,19 @@ void fill_answer_split(pir_db* db, const QueryGeom& g, AnswerPlan* ap, bool thro
     ap->D = db->split_d;
     ap->hi_warps = db->split_hiw;
     ap->Dmin = db->split_dmin;
+    ap->m_task = 0;
+    if (ap->hi_warps != 0u && !throughput) {
+        // Trim the tasks so that every SM gets the same number of rows: 2^24 rows in (7, 12) tasks of 114 688 rows are
+        // 146.3 tasks, i.e. 147 CTAs of which one is a third full and one SM idle; 148 tasks of 443 (instead of 448)
+        // thread-root nodes do 1 % less work each.  Only a light trim: the trailing threads of a task idle.
+        const uint64_t t0 = g.first_row & ~((2ull << ap->D) - 1ull);
+        const uint64_t nodes = (g.first_row + g.n_rows - t0 + (2ull << ap->D) - 1ull) >> (ap->D + 1u);
+        const uint64_t nom = answer_task_nodes(ap->hi_warps, 0);
+        const uint64_t nt = (nodes + nom - 1) / nom, sms = (uint64_t)db->ctx->num_sms;
+        const uint64_t slots = (nt + sms - 1) / sms * sms;
+        const uint64_t m = (nodes + slots - 1) / slots;
+        if (m < nom && 8 * m >= 7 * nom) ap->m_task = (uint32_t)m;
+    }
     // Slices of 8 rows per thread, or of 4 when the task a CTA ends with is shallow: the rows of the last slice
     // are scanned after the tree warps are done, and with 32 rows per thread that slice is a quarter of the task.
     ap->slog_cap = (ap->hi_warps != 0u && ap->D <= 4u) ? 2u : 3u;
@@ -958,6 +990,12 @@ int enqueue_batch_fused(pir_db* db, const pir_query* qs, uint32_t n, const Query
     return rc;
 }
 
+// Can a single query be answered by ONE launch of the warp-specialised kernel (AnswerPlan::final_out)?
+bool single_launch_ok(const pir_db* db, const pir_query* q, const QueryGeom& g) {
+    return !db->tune.host_copy_path && !db->tune.kernel_v1 && !q->is_keyword && g.n_rows != 0 &&
+           answer_kernel_supports(g.row_bytes, 0) && g.row_bytes <= kAnswerMaxRowBytes && !dev_phase_debug_on();
+}
+
 void compact_answer(const pir_db* db, uint32_t W, const uint8_t* pitched, uint8_t* dense) {
     for (uint32_t c = 0; c < W; c++) memcpy(dense + (size_t)c * db->slot_bytes, pitched + (size_t)c * db->pitch, db->slot_bytes);
 }
@@ -978,6 +1016,10 @@ extern "C" int pir_answer_batch_device(pir_db* db, const pir_query* qs, uint32_t
         if (qs[i].group_size != qs[0].group_size || qs[i].is_keyword != qs[0].is_keyword)
             return fail(PIR_ERR_BAD_ARG, "all queries of a batch must share group_size and is_keyword");
     }
+    // One index query: one launch, no memset (the last CTA moves the answer from the handle's accumulator to d_out),
+    // so back-to-back calls on one stream overlap as programmatic dependent launches.
+    if (n_queries == 1 && single_launch_ok(db, &qs[0], g0))
+        return enqueue_answer(db, &qs[0], g0, db->d_acc, st, /*zero_first=*/false, nullptr, nullptr, false, (uint32_t*)d_out);
     if (batch_uses_bits_path(db, qs, n_queries, g0)) return enqueue_batch_bits(db, qs, n_queries, g0, (uint8_t*)d_out, st);
     return enqueue_batch_fused(db, qs, n_queries, g0, (uint8_t*)d_out, st);
 }
@@ -1000,18 +1042,13 @@ extern "C" int pir_answer_batch(pir_db* db, const pir_query* qs, uint32_t n_quer
     }
     // One index query answered by the warp-specialised kernel: its last CTA writes the answer straight into the pinned
     // host buffer and re-zeroes the device accumulator, so the call is one launch and one stream synchronisation.
-    if (n_queries == 1 && !db->tune.host_copy_path && !db->tune.kernel_v1 && db->h_out_dev && !qs[0].is_keyword &&
-        g0.n_rows != 0 && answer_kernel_supports(g0.row_bytes, 0) && !dev_phase_debug_on()) {
-        if (!db->out_zeroed) CU(cudaMemsetAsync(db->d_out, 0, db->out_cap, db->stream));
-        db->out_zeroed = false;
-        rc = enqueue_answer(db, &qs[0], g0, db->d_out, db->stream, /*zero_first=*/false, nullptr, nullptr, false, db->h_out_dev);
+    if (n_queries == 1 && db->h_out_dev && single_launch_ok(db, &qs[0], g0)) {
+        rc = enqueue_answer(db, &qs[0], g0, db->d_acc, db->stream, /*zero_first=*/false, nullptr, nullptr, false, db->h_out_dev);
         if (cudaStreamSynchronize(db->stream) != cudaSuccess && rc == PIR_OK) rc = fail(PIR_ERR_CUDA, "answer kernel failed: %s", cudaGetErrorString(cudaGetLastError()));
         if (rc) return rc;
-        db->out_zeroed = true;
         compact_answer(db, g0.W, db->h_out, (uint8_t*)out);
         return PIR_OK;
     }
-    db->out_zeroed = false;
     if (batch_uses_bits_path(db, qs, n_queries, g0)) {
         if ((rc = enqueue_batch_bits(db, qs, n_queries, g0, db->d_out, db->stream))) {
             cudaStreamSynchronize(db->stream);
@@ -1123,7 +1160,6 @@ extern "C" int pir_answer_with_bits(pir_db* db, uint32_t group_size, const uint8
     const uint64_t row_bytes = (uint64_t)group_size * db->pitch;
     if ((rc = ensure_out(db, row_bytes))) return rc;
     if ((rc = ensure_bits(db, n_rows ? n_rows : 1))) return rc;
-    db->out_zeroed = false;
     CU(cudaMemsetAsync(db->d_out, 0, row_bytes, db->stream));
     if (n_rows) {
         CU(cudaMemcpyAsync(db->d_bits, bits, n_rows, cudaMemcpyHostToDevice, db->stream));
@@ -1776,6 +1812,14 @@ extern "C" int pir_server_answer_batch(pir_server* s, const pir_query* qs, uint3
 
 extern "C" int pir_server_answer(pir_server* s, const pir_query* q, void* out, size_t out_len) {
     return pir_server_answer_batch(s, q, 1, out, out_len);
+}
+extern "C" int pir_debug_current_device(void) {  // (tests: no entry point may change the caller's current device)
+    int d = -1;
+    if (cudaGetDevice(&d) != cudaSuccess) {
+        cudaGetLastError();
+        return -1;
+    }
+    return d;
 }
 extern "C" void pir_debug_answer_split(uint32_t nb, uint64_t first_row, uint64_t n_rows, int num_sms, uint32_t* Dmax,
                                        uint32_t* Dmin, uint32_t* B) {

@@ -42,6 +42,8 @@ struct AnswerPlan {
     uint32_t hi_warps;    //   warps own 2^(D+1) rows each, the others 2^D; hi_warps = 4, 8, 12 or 16 (16 if D = 0).
     uint32_t Dmin;        // binary (hi_warps == 0): chunks of 2^(10+Dmin) rows covered by aligned tasks of depth Dmin..D
     uint32_t pad;         // 0 (PIRB_DEV build: experiment flags, dev_hooks.cuh)
+    uint32_t m_task;      // uniform split: level-L nodes (2^(D+1) rows) per task if fewer than the shape's own (0 = the shape's):
+    uint32_t pad2;        //   tasks trimmed so that all SMs get the same number of rows
     uint32_t slog_cap;    // log2(rows per thread per slice) at most: 3, or 2 when tasks are so shallow that the last
     uint32_t top_warp;    //   slice (whose rows are scanned after the tree warps are done) would be a large part of a CTA's work
                           // top_warp != 0: an extra warp walks the top of task k+1 during the depth-first phase of task k
@@ -55,10 +57,10 @@ struct AnswerPlan {
     // partial has been XORed into `out` (which may be peer memory); cta_done is a zeroed counter in local memory
     uint32_t* arrivals;
     uint32_t* cta_done;
-    // single-GPU host call (optional): the launch's last CTA moves the finished answer from `out` to this mapped
-    // pinned host buffer and leaves `out` zeroed for the next query -- no memset before and no copy after the kernel.
-    // Needs cta_done; not combined with `arrivals`.
-    uint32_t* host_out;
+    // single-GPU call (optional): the launch's last CTA moves the finished answer from `out` to this buffer (device
+    // memory or a mapped pinned host buffer) and leaves `out` zeroed for the next query -- no memset before and no
+    // copy after the kernel.  Needs cta_done; not combined with `arrivals`.
+    uint32_t* final_out;
 };
 
 // The in-kernel phase counters (clock64 / globaltimer) and the experiment flags exist in the PIRB_DEV build only
@@ -125,10 +127,13 @@ cudaError_t configure_kernels();
 // warp-specialised fused expand+scan kernel (answer_kernel.cu)
 bool answer_kernel_supports(uint64_t row_bytes, uint32_t D);
 cudaError_t configure_answer_kernel();
-uint64_t answer_tasks(uint64_t first_row, uint64_t n_rows, uint32_t D, uint32_t hi_warps);  // tasks of a uniform split
+uint64_t answer_tasks(uint64_t first_row, uint64_t n_rows, uint32_t D, uint32_t hi_warps, uint32_t m_task = 0);  // tasks of a uniform split
+uint32_t answer_task_nodes(uint32_t hi_warps, uint32_t m_task);  // level-L nodes per task of a uniform split
 uint64_t answer_chunks(uint64_t first_row, uint64_t n_rows, uint32_t Dmin);                  // chunks of a binary split
+// overlap: programmatic dependent launch (the kernel's CTAs may start while the previous kernel in the stream drains;
+// all its global writes wait for that kernel's completion)
 cudaError_t launch_answer(const QueryConst& qc, const AnswerPlan& ap, const uint32_t* d_t0, uint32_t smem_base,
-                          int num_sms, cudaStream_t st);
+                          int num_sms, cudaStream_t st, bool overlap = false);
 
 // packed bits (bit i = row i) -> one 0/1 byte per row; `bytes` must be 4-byte aligned
 cudaError_t launch_unpack_bits(const uint32_t* packed, uint8_t* bytes, uint64_t n_rows, cudaStream_t st);

@@ -153,3 +153,21 @@ def test_row_range_expansion_matches_full():
     for r0, cnt in ((0, 1), (17, 1000), (4096, 904), (4999, 1)):
         assert np.array_equal(oracle.expand_tree(o0, n, r0, cnt), full[r0:r0 + cnt])
         assert np.array_equal(oracle.expand_shared_query(o0, n, row_begin=r0, n_rows=cnt), full[r0:r0 + cnt])
+
+
+def test_go_vectors_if_present():
+    """tools/go_vectors writes tests/golden/go_vectors.json from the UNMODIFIED Go `dpf` package (crypto/rand replaying
+    the same tapes).  It cannot run where this repo was built (no Go toolchain), so the test skips while the file is
+    absent; once present, every key, Evaluate2P value, selection bit and answer byte must equal the committed vectors
+    that pin the oracle."""
+    path = os.path.join(os.path.dirname(__file__), "golden", "go_vectors.json")
+    if not os.path.exists(path):
+        pytest.skip("tests/golden/go_vectors.json not generated (needs a Go toolchain: tools/go_vectors/run.sh)")
+    go = json.load(open(path))
+    for kind, keys in (("pir", ("num_bits", "query0", "query1", "bits0_packed_le", "bits1_packed_le", "answer0", "answer1")),
+                       ("dpf", ("query0", "query1", "values0", "values1"))):
+        theirs = {c["name"]: c for c in go[kind]}
+        assert set(theirs) == {c["name"] for c in GOLDEN[kind]}
+        for ours in GOLDEN[kind]:
+            for k in keys:
+                assert theirs[ours["name"]][k] == ours[k], (kind, ours["name"], k)
