@@ -198,6 +198,13 @@ int pir_answer_accumulate_device(pir_db* db, const pir_query* q, pir_combine* c,
  * slot, then copy its first out_len bytes to host memory.  PIR_ERR_CUDA on timeout. */
 int pir_combine_wait_read(pir_combine* c, uint32_t slot, uint32_t expected, void* out, size_t out_len,
                           uint32_t timeout_ms);
+/* Owner only: the same wait, then the slot and its arrival counter are zeroed behind the copy (one synchronisation):
+ * on return the slot is free for its next query. */
+int pir_combine_wait_read_reset(pir_combine* c, uint32_t slot, uint32_t expected, void* out, size_t out_len,
+                                uint32_t timeout_ms);
+/* Owner only: enqueue the (device-side, bounded) wait for `expected` arrivals on `stream` (NULL = the combine's own)
+ * and return; work enqueued on that stream afterwards sees the combined answer in the slot. */
+int pir_combine_wait_device(pir_combine* c, uint32_t slot, uint32_t expected, uint32_t timeout_ms, void* stream);
 /* Device address of a slot in this process (for device-resident consumers / tests). */
 void* pir_combine_slot_ptr(pir_combine* c, uint32_t slot);
 
@@ -240,6 +247,10 @@ uint32_t pir_num_bits_for(uint64_t db_size, uint32_t group_size, int is_keyword)
  * summed duration and count, and resets the recorder. */
 int pir_db_set_kernel_timing(pir_db* db, int enable);
 int pir_db_get_kernel_timing(pir_db* db, double* total_ms, uint64_t* launches);
+
+/* The AES-only rate of a shard, measured: average duration of `reps` launches of the answer kernel in BITS mode (the
+ * same tree expansion with the same work split, no database row read), for bench.py's lookup-pipe roofline. */
+int pir_db_time_expansion(pir_db* db, const pir_query* q, uint32_t reps, double* ms_per_launch);
 
 /* counters for benchmarking: number of kernel launches issued by this library in this process */
 uint64_t pir_kernel_launch_count(void);

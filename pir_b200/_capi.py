@@ -31,7 +31,8 @@ EXPORTS = [
     "pir_answer", "pir_answer_batch", "pir_expand_bits", "pir_answer_with_bits",
     "pir_answer_batch_device", "pir_dpf_eval_points", "pir_xor_combine", "pir_num_bits_for",
     "pir_kernel_launch_count", "pir_client_gen_two_server",
-    "pir_db_set_kernel_timing", "pir_db_get_kernel_timing",
+    "pir_db_set_kernel_timing", "pir_db_get_kernel_timing", "pir_db_time_expansion",
+    "pir_combine_wait_read_reset", "pir_combine_wait_device",
     "pir_server_create", "pir_server_destroy", "pir_server_num_shards", "pir_server_shard",
     "pir_server_upload", "pir_server_fill_synthetic", "pir_server_set_keywords", "pir_server_set_option", "pir_server_answer", "pir_server_answer_batch",
     "pir_combine_create", "pir_combine_export", "pir_combine_open", "pir_combine_destroy",
@@ -155,6 +156,9 @@ def lib():
     L.pir_combine_reset.argtypes = [vp, C.c_uint32, C.c_uint32]
     L.pir_answer_accumulate_device.argtypes = [vp, qp, vp, C.c_uint32, vp]
     L.pir_combine_wait_read.argtypes = [vp, C.c_uint32, C.c_uint32, vp, C.c_size_t, C.c_uint32]
+    L.pir_combine_wait_read_reset.argtypes = [vp, C.c_uint32, C.c_uint32, vp, C.c_size_t, C.c_uint32]
+    L.pir_combine_wait_device.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, vp]
+    L.pir_db_time_expansion.argtypes = [vp, qp, C.c_uint32, C.POINTER(C.c_double)]
     L.pir_combine_slot_ptr.argtypes = [vp, C.c_uint32]
     L.pir_combine_slot_ptr.restype = vp
     L.pir_audit_shared_query.argtypes = [vp, qp, vp, C.c_size_t, vp, C.c_size_t]

@@ -1145,6 +1145,54 @@ extern "C" int pir_expand_bits(pir_db* db, const pir_query* q, uint8_t* bits_out
     return PIR_OK;
 }
 
+// The AES-only rate of this shard, measured: `reps` launches of the answer kernel in BITS mode (the same tree
+// expansion for the same work split, selection bits OR-ed into a packed vector, no database row read) between two
+// CUDA events on the handle's stream.  bench.py's lookup-pipe roofline divides by this.
+extern "C" int pir_db_time_expansion(pir_db* db, const pir_query* q, uint32_t reps, double* ms_per_launch) {
+    if (!db || !q || !ms_per_launch || reps == 0) return fail(PIR_ERR_BAD_ARG, "null or empty argument");
+    std::lock_guard<std::mutex> lk(db->mu);
+    DeviceGuard g(db->device);
+    QueryGeom geom;
+    int rc = query_geom(db, q, &geom);
+    if (rc) return rc;
+    if (q->is_keyword || geom.n_rows == 0) return fail(PIR_ERR_BAD_ARG, "needs an index query over a non-empty shard");
+    QueryConst qc;
+    if ((rc = build_query_const(q, geom.nb, &qc))) return rc;
+    const DeviceCtx& ctx = *db->ctx;
+    const uint64_t wpq = (((geom.n_rows + 31) >> 5) + 1 + 3) & ~3ull;
+    if (wpq > db->bitmat_cap) {
+        if (db->d_bitmat) cudaFree(db->d_bitmat);
+        db->d_bitmat = nullptr;
+        db->bitmat_cap = 0;
+        CU(cudaMalloc(&db->d_bitmat, wpq * 4));
+        db->bitmat_cap = wpq;
+    }
+    AnswerPlan ap{};
+    ap.db = db->d_slots;
+    ap.row_bytes = 16;
+    fill_answer_split(db, geom, &ap);
+    ap.bits_out = db->d_bitmat;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    CU(cudaEventCreate(&e0));
+    cudaError_t e = cudaEventCreate(&e1);
+    if (e == cudaSuccess) e = cudaMemsetAsync(db->d_bitmat, 0, wpq * 4, db->stream);
+    if (e == cudaSuccess) e = launch_answer(qc, ap, ctx.d_t0, ctx.smem_base, ctx.num_sms, db->stream);  // warm-up
+    if (e == cudaSuccess) e = cudaEventRecord(e0, db->stream);
+    for (uint32_t i = 0; i < reps && e == cudaSuccess; i++) e = launch_answer(qc, ap, ctx.d_t0, ctx.smem_base, ctx.num_sms, db->stream);
+    if (e == cudaSuccess) e = cudaEventRecord(e1, db->stream);
+    if (e == cudaSuccess) e = cudaEventSynchronize(e1);
+    float ms = 0.f;
+    if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    if (e != cudaSuccess) {
+        cudaStreamSynchronize(db->stream);
+        return fail(PIR_ERR_CUDA, "pir_db_time_expansion: %s", cudaGetErrorString(e));
+    }
+    *ms_per_launch = (double)ms / (double)reps;
+    return PIR_OK;
+}
+
 extern "C" int pir_answer_with_bits(pir_db* db, uint32_t group_size, const uint8_t* bits, uint64_t n_rows,
                                     void* out, size_t out_len) {
     if (!db || (!bits && n_rows) || !out) return fail(PIR_ERR_BAD_ARG, "null argument");
@@ -1538,6 +1586,45 @@ extern "C" int pir_combine_wait_read(pir_combine* c, uint32_t slot, uint32_t exp
     CU(cudaMemcpyAsync(c->h_buf, c->base + (size_t)slot * c->stride, out_len, cudaMemcpyDeviceToHost, c->stream));
     uint32_t* h_flag = (uint32_t*)(c->h_buf + c->stride);
     CU(cudaMemcpyAsync(h_flag, c->timeout_flag(), 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (*h_flag) {
+        cudaMemsetAsync(c->timeout_flag(), 0, 4, c->stream);
+        cudaStreamSynchronize(c->stream);
+        return fail(PIR_ERR_CUDA, "timed out after %u ms waiting for %u shard arrivals at combine slot %u", timeout_ms,
+                    expected, slot);
+    }
+    memcpy(out, c->h_buf, out_len);
+    return PIR_OK;
+}
+
+// Owner only: enqueue the wait for `expected` arrivals at `slot` on `stream` (device-side, bounded) and return.
+extern "C" int pir_combine_wait_device(pir_combine* c, uint32_t slot, uint32_t expected, uint32_t timeout_ms, void* stream) {
+    if (!c) return fail(PIR_ERR_BAD_ARG, "null handle");
+    if (!c->owner) return fail(PIR_ERR_BAD_ARG, "only the owner waits on combine slots");
+    if (slot >= c->n_slots) return fail(PIR_ERR_BAD_ARG, "slot out of range");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->device);
+    const uint64_t cycles = (uint64_t)(c->clock_khz > 0 ? c->clock_khz : 1000000) * (timeout_ms ? timeout_ms : 1);
+    CU(launch_wait_arrivals(c->arrivals(slot), expected, cycles, c->timeout_flag(), stream ? (cudaStream_t)stream : c->stream));
+    return PIR_OK;
+}
+
+// Owner only: pir_combine_wait_read, then the slot and its arrival counter are zeroed behind the copy on the same
+// stream, with ONE synchronisation: on return the slot is free for the next query.
+extern "C" int pir_combine_wait_read_reset(pir_combine* c, uint32_t slot, uint32_t expected, void* out, size_t out_len,
+                                           uint32_t timeout_ms) {
+    if (!c || !out) return fail(PIR_ERR_BAD_ARG, "null argument");
+    if (!c->owner) return fail(PIR_ERR_BAD_ARG, "only the owner reads combine slots");
+    if (slot >= c->n_slots || out_len > c->stride) return fail(PIR_ERR_BAD_ARG, "slot or length out of range");
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->device);
+    const uint64_t cycles = (uint64_t)(c->clock_khz > 0 ? c->clock_khz : 1000000) * (timeout_ms ? timeout_ms : 1);
+    CU(launch_wait_arrivals(c->arrivals(slot), expected, cycles, c->timeout_flag(), c->stream));
+    CU(cudaMemcpyAsync(c->h_buf, c->base + (size_t)slot * c->stride, out_len, cudaMemcpyDeviceToHost, c->stream));
+    uint32_t* h_flag = (uint32_t*)(c->h_buf + c->stride);
+    CU(cudaMemcpyAsync(h_flag, c->timeout_flag(), 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemsetAsync(c->base + (size_t)slot * c->stride, 0, c->stride, c->stream));
+    CU(cudaMemsetAsync(c->arrivals(slot), 0, 4, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     if (*h_flag) {
         cudaMemsetAsync(c->timeout_flag(), 0, 4, c->stream);

@@ -154,6 +154,16 @@ class Combine:
                                                  timeout_ms))
         return out
 
+    def wait_read_reset(self, slot, expected, nbytes, timeout_ms=10000):
+        """wait_read, then the slot is zeroed behind the copy (one synchronisation): free for its next query"""
+        out = np.zeros(nbytes, dtype=np.uint8)
+        _capi.check(self.L.pir_combine_wait_read_reset(self.h, slot, expected, out.ctypes.data_as(C.c_void_p), nbytes,
+                                                       timeout_ms))
+        return out
+
+    def wait_device(self, slot, expected, stream=None, timeout_ms=10000):
+        _capi.check(self.L.pir_combine_wait_device(self.h, slot, expected, timeout_ms, stream))
+
     def close(self):
         if self.h:
             self.L.pir_combine_destroy(self.h)
