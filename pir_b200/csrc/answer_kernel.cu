@@ -372,7 +372,8 @@ __device__ __forceinline__ void build_task_list(const AnswerPlan& ap, uint32_t* 
 // Near the root only a few nodes exist, so three warps on three SMSPs each take ONE AES block of the
 // same node and write their part of the children straight into shared memory:
 //   block 0 -> sL;  block 1 -> tL and bytes 0..14 of sR;  block 2 -> byte 15 of sR and tR.
-__device__ __forceinline__ void coop_block(const QueryConst& qc, uint32_t k, uint4 sv, uint32_t t, uint32_t level,
+template <class QC>
+__device__ __forceinline__ void coop_block(const QC& qc, uint32_t k, uint4 sv, uint32_t t, uint32_t level,
                                            uint32_t lc, uint8_t* left_s, uint8_t* left_t, uint8_t* right_s,
                                            uint8_t* right_t) {
     const uint32_t s[4] = {sv.x, sv.y, sv.z, sv.w};
@@ -420,11 +421,13 @@ __device__ __forceinline__ void coop_block(const QueryConst& qc, uint32_t k, uin
 // rounds; every level is also stored to path_s/path_t, off the critical path, for the restart of later tasks.
 // Round keys come from shared memory (conflict-free: the twelve words of a round lie in twelve banks).
 // Levels [l0, l1) of the walk towards node `a` of level L; path_s[l0], path_t[l0] hold the start node.
-__device__ __forceinline__ void quad_path_walk(const QueryConst& qc, uint32_t lc, uint64_t a, uint32_t L, uint32_t l0, uint32_t l1,
-                                               uint4* path_s, uint8_t* path_t, unsigned long long* dbg = nullptr) {
+// (QC: QueryConst, or the LaConst of the NEXT query for the look-ahead; rk_base: the [3][44] round keys in shared memory)
+template <class QC>
+__device__ __forceinline__ void quad_path_walk(const QC& qc, const uint32_t* rk_base, uint32_t lc, uint64_t a, uint32_t L, uint32_t l0,
+                                               uint32_t l1, uint4* path_s, uint8_t* path_t, unsigned long long* dbg = nullptr) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t c = lane & 3u, k = (lane >> 2) % 3u, g0 = lane & ~3u;  // (lanes 12..31 run along and store nothing)
-    const uint32_t* rk = reinterpret_cast<const uint32_t*>(g_smem2 + kOffRk) + k * 44u + c;
+    const uint32_t* rk = rk_base + k * 44u + c;
     uint32_t sw = reinterpret_cast<const uint32_t*>(&path_s[l0])[c];
     uint32_t t = path_t[l0];
     for (uint32_t l = l0; l < l1; l++) {
@@ -608,6 +611,117 @@ struct TopWalker {
     }
 };
 
+// ---- look-ahead: the top of the NEXT launch's task, by this launch's walker warp (kernels.cuh LaMail / LaTop) -----
+__device__ __forceinline__ uint64_t ld_acquire_sys_u64(const uint64_t* p) {
+    uint64_t v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint64_t ld_acquire_gpu_u64(const uint64_t* p) {
+    uint64_t v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_gpu_u64(uint64_t* p, uint64_t v) {
+    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_relaxed_sys_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+constexpr uint32_t kOffLaConst = kOffPath2S;  // the walker's own path arrays are idle while a CTA has a single task
+static_assert(sizeof(LaConst) <= 65 * 16 + 80, "LaConst must fit the walker's path arrays");
+static_assert(kLaHand == kHand, "hand-over width");
+
+// One warp.  Returns true when there is nothing (more) to do for this launch: the next launch's top has been written,
+// or its mail has a different shape / has been overwritten; false if the mail has not arrived yet (poll again later).
+// Only called by the walker warp of a CTA with exactly one task: its scratch (walker path arrays, level buffer and the
+// hand-over double buffer) is otherwise idle.
+__device__ __noinline__ bool lookahead_next_top(const AnswerPlan& ap, uint32_t top_bits) {
+    const uint32_t lane = threadIdx.x & 31u, lc = lane_const();
+    const uint64_t next = ap.la_seq + 1ull;
+    const LaMail* mail = ap.la_mail + (next % kLaMailRing);
+    // seqlock: tag, payload, tag again (the host writes 0, payload, tag; it may be re-using the entry for launch next + 64)
+    uint64_t tag = 0, geom = 0;
+    if (lane == 0) {
+        tag = ld_acquire_sys_u64(&mail->tag);
+        geom = tag == next ? ld_acquire_sys_u64(&mail->geom) : 0ull;
+    }
+    tag = __shfl_sync(0xffffffffu, tag, 0);
+    geom = __shfl_sync(0xffffffffu, geom, 0);
+    if (tag != next) return tag > next;          // not there yet (poll again) / already overwritten (give up)
+    if (geom != ap.la_geom) return true;         // the next launch has another shape: its CTAs walk their own tops
+    LaConst* la = reinterpret_cast<LaConst*>(g_smem2 + kOffLaConst);
+    {
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(&mail->c);
+        uint32_t* dst = reinterpret_cast<uint32_t*>(la);
+        for (uint32_t w = lane; w < sizeof(LaConst) / 4u; w += 32u) dst[w] = ld_relaxed_sys_u32(src + w);
+    }
+    __syncwarp();
+    asm volatile("fence.acq_rel.sys;" ::: "memory");
+    uint64_t tag2 = lane == 0 ? ld_acquire_sys_u64(&mail->tag) : 0ull;
+    tag2 = __shfl_sync(0xffffffffu, tag2, 0);
+    if (tag2 != next) return true;               // torn read: give up
+    const uint32_t dyn_base = smem_addr(g_smem2);
+    const TaskIter ti(reinterpret_cast<const uint32_t*>(g_smem2 + kOffTasks));
+    TaskShape ts;
+    uint64_t row_start;
+    ti.decode(0u, row_start, ts);
+    const TaskTop tt(ts, row_start, top_bits);
+    if (tt.Lh > kLaMaxLevels) return true;       // (correction words of deeper levels are not in the mail)
+    // single-node levels 0 .. Ls: path arrays in the walker's level scratch
+    uint4* path_s = reinterpret_cast<uint4*>(g_smem2 + kOffTopScrS);  // [kHand] uint4 >= [65]
+    uint8_t* path_t = g_smem2 + kOffTopScrT;                          // [kHand] u8
+    if (lane == 0) {
+        path_s[0] = make_uint4(la->s_init[0], la->s_init[1], la->s_init[2], la->s_init[3]);
+        path_t[0] = (uint8_t)la->t_init;
+    }
+    __syncwarp();
+    quad_path_walk(*la, &la->rk[0][0], lc, tt.a, tt.L, 0u, tt.Ls, path_s, path_t);
+    // breadth-first levels Ls .. Lh-1 between the two hand-over buffers (3 lanes per node, 10 nodes per pass)
+    uint4* hb_s[2] = {reinterpret_cast<uint4*>(g_smem2 + (kAbsHandS - dyn_base)), reinterpret_cast<uint4*>(g_smem2 + (kAbsHandS - dyn_base)) + kHand};
+    uint8_t* hb_t[2] = {g_smem2 + (kAbsHandT - dyn_base), g_smem2 + (kAbsHandT - dyn_base) + kHand};
+    const uint32_t k = lane % 3u, jl = lane / 3u;
+    for (uint32_t l = tt.Ls; l < tt.Lh; l++) {
+        const uint4* ss = l == tt.Ls ? &path_s[l] : hb_s[l & 1u];
+        const uint8_t* st = l == tt.Ls ? &path_t[l] : hb_t[l & 1u];
+        uint4* ds = hb_s[(l + 1u) & 1u];
+        uint8_t* dt = hb_t[(l + 1u) & 1u];
+        const uint32_t sh = tt.L - l;
+        const uint64_t lo = tt.a >> sh, lo2 = tt.a >> (sh - 1u);
+        const uint32_t n = nodes_at(tt.L, tt.a, tt.m, l), n2 = nodes_at(tt.L, tt.a, tt.m, l + 1u);
+        const uint32_t skip = (uint32_t)(lo2 - 2ull * lo);
+        for (uint32_t j0 = 0; j0 < n; j0 += 10u) {
+            const uint32_t j = j0 + jl;
+            if (lane < 30u && j < n) {
+                const uint32_t li = 2u * j - skip, ri = li + 1u;
+                const bool lv = (j > 0u || skip == 0u) && li < n2, rv = ri < n2;
+                coop_block(*la, k, ss[j], st[j], l, lc, lv ? reinterpret_cast<uint8_t*>(&ds[li]) : nullptr, lv ? &dt[li] : nullptr,
+                           rv ? reinterpret_cast<uint8_t*>(&ds[ri]) : nullptr, rv ? &dt[ri] : nullptr);
+            }
+        }
+        __syncwarp();
+    }
+    const uint4* fs = tt.Lh == tt.Ls ? &path_s[tt.Ls] : hb_s[tt.Lh & 1u];
+    const uint8_t* ft = tt.Lh == tt.Ls ? &path_t[tt.Ls] : hb_t[tt.Lh & 1u];
+    const uint32_t n = nodes_at(tt.L, tt.a, tt.m, tt.Lh);
+    LaTop* out = ap.la_tops + (next % kLaTopRing) * gridDim.x + blockIdx.x;
+    for (uint32_t j = lane; j < n; j += 32u) {
+        out->seed[j] = fs[j];
+        out->t[j] = ft[j];
+    }
+    __threadfence();
+    __syncwarp();
+    if (lane == 0) {
+        out->n = n;
+        out->lh = tt.Lh;
+        st_release_gpu_u64(&out->ready, next);
+    }
+    __syncwarp();
+    return true;
+}
+
 // ---- consumer loop (scan warps all along, tree warps once they have nothing left to expand) ----------
 // Work unit = one 32-word group of one slice, claimed in order from a shared counter, so the backlog at
 // the end of the kernel is drained by all 20 warps.  The warp that completes a slice's last group hands
@@ -628,6 +742,12 @@ __device__ __forceinline__ void consume_slices(const QueryConst& qc, const Answe
     for (int cb = 0; cb < NCB; cb++) acc[cb] = make_uint4(0, 0, 0, 0);
     long long c_wait = 0;
     const long long c_in = PIRB_AP_DBG(ap) ? clock64() : 0;
+    // Look-ahead (DUAL warp of a CTA with one task, ap.la_mail set): before the first slice arrives the scan warps
+    // idle anyway, so that is when the next launch's top is walked; if its mail is not there yet, poll again after
+    // 16, 64 and 256 scan units.
+    bool la_todo = DUAL && ap.la_mail != nullptr && ti.n == 1u;
+    uint32_t la_units = 0, la_next = 16u;
+    if (la_todo) la_todo = !lookahead_next_top(ap, qc.num_bits - 1u);
     // DUAL: this scan warp also walks the tops of the tasks ahead (TopWalker), before anything else whenever a
     // hand-over buffer is free -- the tree warps will wait for it at the next task boundary, the scan has slack.
     while (true) {
@@ -645,6 +765,10 @@ __device__ __forceinline__ void consume_slices(const QueryConst& qc, const Answe
             gs1 += 1u << ti.slices_log(ti.pos++);
         }
         if (!have) break;
+        if (la_todo && ++la_units == la_next) {
+            la_next = la_next >= 256u ? 0xffffffffu : la_next * 4u;
+            la_todo = !lookahead_next_top(ap, qc.num_bits - 1u);
+        }
         const uint32_t slot = gsl & (kRing - 1u), par = (gsl / kRing) & 1u;
         const long long cw0 = (PIRB_AP_DBG(ap) && warp_in_cta == kTreeWarps) ? clock64() : 0;
         if (DUAL) {
@@ -733,7 +857,31 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
         //    previous task. --
         const uint32_t Ls = single_node_levels(L, a, m);
         uint32_t l_bfs = Ls;  // first breadth-first level the tree warps expand themselves
-        if (ap.top_warp && it > 0u) {
+        bool la_hit = false;
+        if (it == 0u && n_tasks == 1u && ap.la_tops != nullptr) {
+            // has the launch before this one left this task's top for us (look-ahead)?
+            const uint32_t Lh = hand_level(L, a, m, Ls);
+            volatile uint32_t* flag = reinterpret_cast<volatile uint32_t*>(g_smem2 + kOffPathT + 72);
+            const LaTop* in = ap.la_tops + (ap.la_seq % kLaTopRing) * gridDim.x + blockIdx.x;
+            if (tid == 0) {
+                bool ok = ld_acquire_gpu_u64(&in->ready) == ap.la_seq;
+                if (ok) ok = __ldcg(&in->lh) == Lh && __ldcg(&in->n) == nodes_at(L, a, m, Lh);
+                *flag = ok ? 1u : 0u;
+            }
+            bar_sync(BAR_TREE, kTreeThreads);
+            la_hit = *flag != 0u;
+            if (la_hit) {
+                if (tid < nodes_at(L, a, m, Lh)) {
+                    bfs_s[(Lh & 1u) * kTreeThreads + tid] = __ldcg(&in->seed[tid]);
+                    bfs_t[(Lh & 1u) * kTreeThreads + tid] = __ldcg(&in->t[tid]);
+                }
+                bar_sync(BAR_TREE, kTreeThreads);
+                l_bfs = Lh;
+            }
+        }
+        if (la_hit) {
+            // (nothing to walk)
+        } else if (ap.top_warp && it > 0u) {
             // the top warp has walked this task's top while we were in the previous task's depth-first phase
             const uint32_t Lh = hand_level(L, a, m, Ls);
             const uint32_t buf = it & 1u, use = (it - 1u) >> 1;
@@ -770,7 +918,8 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
                 cp = cp < Ls ? cp : Ls;
             }
             if (warp == 0u) {  // one warp walks the whole chain, the node stays in registers (no CTA barrier per level)
-                quad_path_walk(qc, lc, a, L, cp, Ls, path_s, path_t, (PIRB_AP_DBG(ap) && blockIdx.x == 0 && it == 0) ? PIRB_AP_DBG(ap) : nullptr);
+                quad_path_walk(qc, reinterpret_cast<const uint32_t*>(g_smem2 + kOffRk), lc, a, L, cp, Ls, path_s, path_t,
+                               (PIRB_AP_DBG(ap) && blockIdx.x == 0 && it == 0) ? PIRB_AP_DBG(ap) : nullptr);
                 if (lane == 0) {
                     bfs_s[(Ls & 1u) * kTreeThreads] = path_s[Ls];
                     bfs_t[(Ls & 1u) * kTreeThreads] = path_t[Ls];

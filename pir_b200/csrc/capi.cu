@@ -7,6 +7,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <atomic>
+#include <initializer_list>
 #include <mutex>
 #include <new>
 #include <vector>
@@ -225,6 +227,7 @@ struct Tuning {
     bool signal_kernel = false;   // multi-GPU: separate arrival kernel instead of the answer kernel's last CTA
     bool host_copy_path = false;  // pir_answer: memset + kernel + copy instead of the one-launch host path
     bool serial_launch = false;   // no programmatic dependent launch between consecutive answer kernels
+    bool no_lookahead = false;    // launches do not walk the next launch's tree top (kernels.cuh LaMail)
 };
 
 constexpr uint32_t kCtaDoneRing = 64;
@@ -265,6 +268,11 @@ struct pir_db {
     uint8_t* d_acc = nullptr;
     cudaStream_t acc_stream = nullptr;
     cudaEvent_t acc_ev = nullptr;
+    // look-ahead (kernels.cuh LaMail / LaTop): key material of the launches in the queue, host-mapped; tops in HBM
+    LaMail* h_mail = nullptr;
+    const LaMail* h_mail_dev = nullptr;
+    LaTop* d_tops = nullptr;
+    uint64_t la_seq = 0;
     uint64_t h_out_cap = 0;
     // cached work split of the answer kernel for the last (num_bits, shard rows) seen
     uint32_t split_nb = 0, split_d = 0, split_hiw = 0, split_dmin = 0;
@@ -497,6 +505,16 @@ extern "C" int pir_db_create(int device, uint64_t db_size, uint32_t slot_bytes, 
     if (e == cudaSuccess) e = cudaMalloc(&db->d_cta_done, kCtaDoneRing * sizeof(uint32_t));
     if (e == cudaSuccess) e = cudaMemsetAsync(db->d_cta_done, 0, kCtaDoneRing * sizeof(uint32_t), db->stream);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&db->acc_ev, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaHostAlloc(&db->h_mail, kLaMailRing * sizeof(LaMail), cudaHostAllocMapped);
+    if (e == cudaSuccess) {
+        memset(db->h_mail, 0, kLaMailRing * sizeof(LaMail));
+        void* dp = nullptr;
+        if (cudaHostGetDevicePointer(&dp, db->h_mail, 0) == cudaSuccess) db->h_mail_dev = (const LaMail*)dp;
+        else cudaGetLastError();  // (no mapped access: look-ahead stays off)
+    }
+    const size_t tops_bytes = (size_t)kLaTopRing * (size_t)ctx->num_sms * sizeof(LaTop);
+    if (e == cudaSuccess) e = cudaMalloc(&db->d_tops, tops_bytes);
+    if (e == cudaSuccess) e = cudaMemsetAsync(db->d_tops, 0, tops_bytes, db->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(db->stream);
     if (e != cudaSuccess) {
         int code = e == cudaErrorMemoryAllocation ? PIR_ERR_OOM : PIR_ERR_CUDA;
@@ -522,6 +540,8 @@ extern "C" int pir_db_destroy(pir_db* db) {
     if (db->d_cta_done) cudaFree(db->d_cta_done);
     if (db->d_acc) cudaFree(db->d_acc);
     if (db->acc_ev) cudaEventDestroy(db->acc_ev);
+    if (db->d_tops) cudaFree(db->d_tops);
+    if (db->h_mail) cudaFreeHost(db->h_mail);
     for (int k = 0; k < 2; k++)
         if (db->side[k]) cudaStreamDestroy(db->side[k]);
     for (int k = 0; k < 3; k++)
@@ -577,6 +597,7 @@ int set_tuning(Tuning& t, const char* name, int64_t v) {
         {"signal_kernel", nullptr, &t.signal_kernel, 0, 1},
         {"host_copy_path", nullptr, &t.host_copy_path, 0, 1},
         {"serial_launch", nullptr, &t.serial_launch, 0, 1},
+        {"no_lookahead", nullptr, &t.no_lookahead, 0, 1},
     };
     for (auto& e : tab) {
         if (strcmp(e.n, name)) continue;
@@ -755,6 +776,33 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
             ap.arrivals = arrivals;
             ap.cta_done = db->d_cta_done + (db->cta_done_next++ % kCtaDoneRing);  // reset by the launch's last CTA
             *signalled = true;
+        }
+        // Look-ahead: leave this launch's key material where the launch before it can find it, and tell this launch where
+        // to look for the one after it.  Only for launches of one task per CTA with a walker warp (rows >= 128 B).
+        if (!db->tune.no_lookahead && db->h_mail_dev && ap.top_warp && ap.hi_warps != 0u && g.nb - 1u - ap.D <= kLaMaxLevels &&
+            answer_tasks(ap.first_row, ap.n_rows, ap.D, ap.hi_warps, ap.m_task) <= (uint64_t)ctx.num_sms) {
+            const uint64_t seq = ++db->la_seq;
+            uint64_t hsh = 0x9E3779B97F4A7C15ull;
+            for (uint64_t v : {(uint64_t)g.nb, (uint64_t)ap.D, (uint64_t)ap.hi_warps, (uint64_t)ap.m_task, (uint64_t)ap.slog_cap, ap.first_row,
+                               ap.n_rows, (uint64_t)g.row_bytes})
+                hsh = (hsh ^ v) * 0xBF58476D1CE4E5B9ull + (hsh >> 29);
+            LaMail* m = db->h_mail + (seq % kLaMailRing);
+            volatile uint64_t* tag = &m->tag;
+            *tag = 0;  // seqlock: invalid while the payload changes (a launch up to 64 back may still poll this entry)
+            std::atomic_thread_fence(std::memory_order_seq_cst);
+            m->geom = hsh;
+            memcpy(m->c.rk, qc.rk, sizeof m->c.rk);
+            memcpy(m->c.cw, qc.cw, sizeof m->c.cw);
+            m->c.cw_tl = qc.cw_tl;
+            m->c.cw_tr = qc.cw_tr;
+            memcpy(m->c.s_init, qc.s_init, sizeof m->c.s_init);
+            m->c.t_init = qc.t_init;
+            std::atomic_thread_fence(std::memory_order_seq_cst);
+            *tag = seq;
+            ap.la_seq = seq;
+            ap.la_geom = hsh;
+            ap.la_mail = db->h_mail_dev;
+            ap.la_tops = db->d_tops;
         }
 #ifdef PIRB_DEV
         DevPhase dev_phase;

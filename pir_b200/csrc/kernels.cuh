@@ -30,6 +30,36 @@ struct FusedPlan {
     uint8_t* bits_out;        // BITS mode: one byte per shard row
 };
 
+// ---- look-ahead of the next query's tree top (answer_kernel.cu "look-ahead") ---------------------------------------
+// The top of a task is a chain of ~20 dependent node expansions that nothing in the SAME query can hide.  Under load
+// the next query of the handle is already enqueued while this one runs, so the host leaves its key material in a
+// host-mapped ring (LaMail, written at enqueue time), the walker warp of launch j computes the top of launch j+1's
+// task for the same CTA and leaves the nodes in global memory (LaTop), and launch j+1 starts from them.  Purely
+// opportunistic: every entry is validated by its sequence number (mail: seqlock; tops: release/acquire), and a
+// launch that finds nothing walks its own top as before.
+constexpr uint32_t kLaMailRing = 64;   // launches the host may run ahead of the GPU before look-ahead stops finding its mail
+constexpr uint32_t kLaTopRing = 4;     // launch j+1's entry is written during launch j and read at the start of j+1
+constexpr uint32_t kLaMaxLevels = 32;  // correction words kept per mail entry (levels above the thread roots)
+constexpr uint32_t kLaHand = 128;      // nodes handed over per CTA (answer_kernel.cu kHand)
+struct LaConst {                       // what a top walk needs of QueryConst; same member names
+    uint32_t rk[3][44];
+    uint32_t cw[kLaMaxLevels][4];
+    uint64_t cw_tl, cw_tr;
+    uint32_t s_init[4];
+    uint32_t t_init, pad;
+};
+struct LaMail {
+    uint64_t tag;    // sequence number of the launch this entry belongs to; 0 while the host is writing it
+    uint64_t geom;   // hash of shard geometry and work split: the top is only valid for an identical launch shape
+    LaConst c;
+};
+struct LaTop {       // one per (ring entry, CTA)
+    uint64_t ready;  // sequence number of the launch these nodes are for
+    uint32_t n, lh;  // nodes, tree level
+    uint4 seed[kLaHand];
+    uint8_t t[kLaHand];
+};
+
 // Geometry of one launch of the warp-specialised answer kernel (answer_kernel.cu).  Same meaning as
 // FusedPlan, but the kernel walks the top of the tree itself (no frontier buffers).
 struct AnswerPlan {
@@ -61,6 +91,11 @@ struct AnswerPlan {
     // memory or a mapped pinned host buffer) and leaves `out` zeroed for the next query -- no memset before and no
     // copy after the kernel.  Needs cta_done; not combined with `arrivals`.
     uint32_t* final_out;
+    // look-ahead (optional, all null / 0 = off): this launch's sequence number on its handle, the hash of its shape,
+    // the host-mapped mail ring [kLaMailRing] and the tops ring [kLaTopRing][gridDim.x] in device memory
+    uint64_t la_seq, la_geom;
+    const LaMail* la_mail;
+    LaTop* la_tops;
 };
 
 // The in-kernel phase counters (clock64 / globaltimer) and the experiment flags exist in the PIRB_DEV build only

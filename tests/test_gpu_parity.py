@@ -366,3 +366,35 @@ def test_both_final_cw_parities_are_covered(gpu_lib):
             assert np.array_equal(a1, oracle.answer(o1, data, db_size, slot_bytes)), (seed, par)
             assert np.array_equal(a0 ^ a1, data[idx])
             assert np.array_equal(h.expand_bits(q0), oracle.expand_shared_query(o0, db_size)), (seed, par)
+
+
+@pytest.mark.parametrize("log_rows,slot_bytes", [(17, 256), (20, 128), (15, 512)])
+def test_back_to_back_launches_with_lookahead_and_overlap(gpu_lib, log_rows, slot_bytes):
+    """Consecutive single-query launches on one stream overlap (programmatic dependent launch) and every launch's
+    walker warp computes the tree top of the launch behind it from the key material the host left in the mail ring
+    (answer_kernel.cu look-ahead).  40 different keys in flight at once, both servers: every answer must equal the
+    oracle's, with the look-ahead and the overlap switched on (default) and off."""
+    import ctypes as C
+    import torch
+    from pir_b200 import _capi
+    n, S = 1 << log_rows, slot_bytes
+    data = oracle.synth_fill(44, 0, n, S)
+    rng = np.random.default_rng(log_rows)
+    pairs = [make_queries(3000 + k, n, 1, int(rng.integers(0, n))) for k in range(20)]
+    keys = [(p[0][s], p[1][s]) for p in pairs for s in (0, 1)]
+    want = np.stack([oracle.answer(o, data, n, S, use_tree=True) for o, _ in keys])
+    st = torch.cuda.Stream()
+    with Handle(n, S) as h:
+        h.fill(44)
+        for opts in ({}, {"no_lookahead": 1}, {"serial_launch": 1}, {"no_lookahead": 1, "serial_launch": 1}):
+            for name in ("no_lookahead", "serial_launch"):
+                h.set_option(name, opts.get(name, 0))
+            for rep in range(3):
+                d_out = torch.zeros((len(keys), S), dtype=torch.uint8, device="cuda")
+                for k, (_, q) in enumerate(keys):
+                    _capi.check(gpu_lib.pir_answer_batch_device(h.h, C.byref(q), 1, C.c_void_p(d_out[k].data_ptr()), C.c_void_p(st.cuda_stream)))
+                st.synchronize()
+                assert np.array_equal(d_out.cpu().numpy(), want), (opts, rep)
+            # the host call (one launch + sync per query) follows the same path one query at a time
+            for k in (0, 1, 39):
+                assert np.array_equal(h.answer(keys[k][1]), want[k])

@@ -5,6 +5,7 @@ import ctypes as C, os, sys, time
 import numpy as np
 sys.path.insert(0, os.getcwd())
 from pir_b200 import _capi
+_capi.use_dev_library()   # PIRB_* switches and phase counters exist in the -DPIRB_DEV build only
 L = _capi.lib()
 n, S, Q = 1 << int(os.environ.get("LOG_ROWS", "22")), int(os.environ.get("SLOT", "1024")), int(os.environ.get("Q", "64"))
 nb = L.pir_num_bits_for(n, 1, 0)

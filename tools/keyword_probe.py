@@ -2,6 +2,7 @@ import ctypes as C, os, sys, time
 import numpy as np
 sys.path.insert(0, os.getcwd())
 from pir_b200 import _capi
+_capi.use_dev_library()   # PIRB_* switches and phase counters exist in the -DPIRB_DEV build only
 L = _capi.lib()
 logn = int(os.environ.get("LOG_ROWS", "24"))
 n, S = 1 << logn, 32

@@ -5,6 +5,7 @@ import numpy as np
 sys.path.insert(0, os.getcwd())
 os.environ["PIRB_DFS_DEPTH"], os.environ["PIRB_HI_WARPS"] = "7", "16"
 from pir_b200 import _capi
+_capi.use_dev_library()   # PIRB_* switches and phase counters exist in the -DPIRB_DEV build only
 L = _capi.lib()
 n, S = 1 << 24, 256
 nb = L.pir_num_bits_for(n, 1, 0)

@@ -4,6 +4,7 @@ import numpy as np
 sys.path.insert(0, os.getcwd())
 from pir_b200 import _capi
 from tools._keys import key_per_parity
+_capi.use_dev_library()   # PIRB_* switches and phase counters exist in the -DPIRB_DEV build only
 L = _capi.lib()
 n, S = 1 << 24, 256
 nb = L.pir_num_bits_for(n, 1, 0)

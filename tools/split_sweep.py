@@ -13,6 +13,8 @@ sys.path.insert(0, ROOT)
 from pir_b200 import _capi  # noqa: E402
 from tools._keys import key_per_parity  # noqa: E402
 
+_capi.use_dev_library()   # PIRB_* switches and phase counters exist in the -DPIRB_DEV build only
+
 L = _capi.lib()
 n, S = 1 << int(os.environ.get("LOG_ROWS", "24")), int(os.environ.get("SLOT", "256"))
 nb = L.pir_num_bits_for(n, 1, 0)
