@@ -125,20 +125,29 @@ __device__ __forceinline__ uint32_t range_mask32(uint64_t rowbase, uint32_t rw, 
 __device__ __forceinline__ uint32_t slice_log(uint32_t d, uint32_t cap) { return d + 1u < cap ? d + 1u : cap; }
 
 // ---- scan: selected rows of 32 words of a slice -> registers ----------------------------------------
+// Rows of any multiple of 16 bytes up to 4 KB.  A row of c 16-byte chunks takes c lanes of a warp load; rpl = the largest
+// power of two <= 32 / c rows are fetched per load (the list is kept as rpl interleaved sub-lists) and the lanes beyond
+// rpl * c idle: none for power-of-two rows, 11 of 32 for 336-byte rows (c = 21), 8 of 32 for 48-byte rows (c = 3,
+// rpl = 8).  Rows wider than a warp load (512 B) are fetched in NCB column blocks of 512 B, the last one partly filled.
 struct ScanLane {
-    uint32_t rpl, h, c;
+    uint32_t rpl, h, c, chunk;
+    uint32_t hsub;           // the sub-list this lane reads its row numbers from
+    bool live;               // this lane fetches (lanes beyond rpl * c idle)
     const uint8_t* lane_db;  // db + this lane's 16-byte chunk
 };
 
 __device__ __forceinline__ ScanLane scan_lane(const AnswerPlan& ap) {
     ScanLane sl;
     const uint32_t lane = threadIdx.x & 31u;
-    sl.c = (uint32_t)(ap.row_bytes >> 4);  // 16-byte chunks per row (power of two); rows wider than a warp
-    if (sl.c > 32u) sl.c = 32u;            // load (512 B) are fetched in NCB column blocks of 512 B
-    const uint32_t logc = 31u - __clz(sl.c);
-    sl.rpl = 32u >> logc;                  // rows per warp load
-    sl.h = lane >> logc;
-    sl.lane_db = ap.db + ((lane & (sl.c - 1u)) << 4);
+    const uint32_t c_row = (uint32_t)(ap.row_bytes >> 4);  // 16-byte chunks per row
+    sl.c = c_row > 32u ? 32u : c_row;
+    sl.rpl = 1u << (31u - __clz(32u / sl.c));              // rows per warp load
+    sl.h = lane / sl.c;
+    sl.chunk = lane - sl.h * sl.c;
+    sl.live = sl.h < sl.rpl;
+    sl.hsub = sl.live ? sl.h : sl.rpl - 1u;                // (idle lanes read a valid sub-list ...
+    if (!sl.live) sl.h = 0x10000u;                         //  ... and their entry numbers lie beyond every list: no load)
+    sl.lane_db = ap.db + (sl.chunk << 4);
     return sl;
 }
 
@@ -175,10 +184,17 @@ __device__ __forceinline__ void scan_group(const AnswerPlan& ap, const ScanLane&
         w &= w - 1u;
     }
     __syncwarp();
-    const uint16_t* sub = list + sl.h * sub_stride;
+    const uint16_t* sub = list + sl.hsub * sub_stride;
 #pragma unroll
     for (int cb = 0; cb < NCB; cb++) {
         const uint8_t* cbase = gbase + cb * 512;
+        // wide rows: the last 512-byte column block may be partly filled (lanes beyond the row's last chunk skip it)
+        uint32_t my_total = total;
+        if (NCB > 1) {
+            const uint32_t c_row = (uint32_t)(ap.row_bytes >> 4);
+            if ((uint32_t)cb * 32u >= c_row) break;
+            if ((uint32_t)cb * 32u + sl.chunk >= c_row) my_total = 0u;
+        }
         for (uint32_t e0 = 0; e0 < ((PIRB_AP_PAD(ap) & 1u) ? 0u : total); e0 += sl.rpl * UNROLL) {
             uint4 v[UNROLL];
 #pragma unroll
@@ -192,7 +208,7 @@ __device__ __forceinline__ void scan_group(const AnswerPlan& ap, const ScanLane&
                     const uint32_t e = eb + (uint32_t)u * sl.rpl + sl.h;
                     const uint32_t row = (lw[u >> 1] >> ((u & 1) * 16)) & 0xffffu;
                     v[k * 8 + u] = make_uint4(0, 0, 0, 0);
-                    if (e < total) v[k * 8 + u] = ldg_nc_v4(cbase + (uint64_t)row * ap.row_bytes);
+                    if (e < my_total) v[k * 8 + u] = ldg_nc_v4(cbase + (uint64_t)row * ap.row_bytes);
                 }
             }
 #pragma unroll
@@ -210,20 +226,24 @@ template <int NCB>
 __device__ __forceinline__ void fold_acc(const ScanLane& sl, uint4 (&accs)[NCB]) {
     const uint32_t lane = threadIdx.x & 31u;
     uint32_t* red = red_words();
+    const bool pow2 = (sl.c & (sl.c - 1u)) == 0u;
 #pragma unroll
     for (int cb = 0; cb < NCB; cb++) {
         uint4 acc = accs[cb];
-        for (uint32_t off = 16; off >= sl.c && off > 0; off >>= 1) {
-            acc.x ^= __shfl_xor_sync(0xffffffffu, acc.x, off);
-            acc.y ^= __shfl_xor_sync(0xffffffffu, acc.y, off);
-            acc.z ^= __shfl_xor_sync(0xffffffffu, acc.z, off);
-            acc.w ^= __shfl_xor_sync(0xffffffffu, acc.w, off);
+        if (pow2) {  // lanes l, l + c, l + 2c ... hold the same chunk: butterfly, then one atomic per chunk
+            for (uint32_t off = 16; off >= sl.c && off > 0; off >>= 1) {
+                acc.x ^= __shfl_xor_sync(0xffffffffu, acc.x, off);
+                acc.y ^= __shfl_xor_sync(0xffffffffu, acc.y, off);
+                acc.z ^= __shfl_xor_sync(0xffffffffu, acc.z, off);
+                acc.w ^= __shfl_xor_sync(0xffffffffu, acc.w, off);
+            }
         }
-        if (lane < sl.c && (acc.x | acc.y | acc.z | acc.w)) {
-            atomicXor(&red[cb * 128 + lane * 4 + 0], acc.x);
-            atomicXor(&red[cb * 128 + lane * 4 + 1], acc.y);
-            atomicXor(&red[cb * 128 + lane * 4 + 2], acc.z);
-            atomicXor(&red[cb * 128 + lane * 4 + 3], acc.w);
+        // (other row sizes: every fetching lane adds its own share; the accumulators of idle lanes are zero)
+        if ((pow2 ? lane < sl.c : sl.live) && (acc.x | acc.y | acc.z | acc.w)) {
+            atomicXor(&red[cb * 128 + sl.chunk * 4 + 0], acc.x);
+            atomicXor(&red[cb * 128 + sl.chunk * 4 + 1], acc.y);
+            atomicXor(&red[cb * 128 + sl.chunk * 4 + 2], acc.z);
+            atomicXor(&red[cb * 128 + sl.chunk * 4 + 3], acc.w);
         }
     }
 }
@@ -638,31 +658,85 @@ static_assert(kLaHand == kHand, "hand-over width");
 // or its mail has a different shape / has been overwritten; false if the mail has not arrived yet (poll again later).
 // Only called by the walker warp of a CTA with exactly one task: its scratch (walker path arrays, level buffer and the
 // hand-over double buffer) is otherwise idle.
-__device__ __noinline__ bool lookahead_next_top(const AnswerPlan& ap, uint32_t top_bits) {
+__device__ __forceinline__ uint64_t ld_relaxed_sys_u64(const uint64_t* p) {
+    uint64_t v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint64_t ld_relaxed_gpu_u64(const uint64_t* p) {
+    uint64_t v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_gpu_u64(uint64_t* p, uint64_t v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+static_assert(sizeof(LaConst) % 8 == 0, "LaConst is copied in 64-bit words");
+
+// `polls`: how often a CTA other than the fetcher looks for the device copy of the mail before it goes on to scan.
+__device__ __noinline__ bool lookahead_next_top(const AnswerPlan& ap, uint32_t top_bits, uint32_t polls) {
     const uint32_t lane = threadIdx.x & 31u, lc = lane_const();
     const uint64_t next = ap.la_seq + 1ull;
-    const LaMail* mail = ap.la_mail + (next % kLaMailRing);
-    // seqlock: tag, payload, tag again (the host writes 0, payload, tag; it may be re-using the entry for launch next + 64)
-    uint64_t tag = 0, geom = 0;
-    if (lane == 0) {
-        tag = ld_acquire_sys_u64(&mail->tag);
-        geom = tag == next ? ld_acquire_sys_u64(&mail->geom) : 0ull;
-    }
-    tag = __shfl_sync(0xffffffffu, tag, 0);
-    geom = __shfl_sync(0xffffffffu, geom, 0);
-    if (tag != next) return tag > next;          // not there yet (poll again) / already overwritten (give up)
-    if (geom != ap.la_geom) return true;         // the next launch has another shape: its CTAs walk their own tops
     LaConst* la = reinterpret_cast<LaConst*>(g_smem2 + kOffLaConst);
-    {
-        const uint32_t* src = reinterpret_cast<const uint32_t*>(&mail->c);
-        uint32_t* dst = reinterpret_cast<uint32_t*>(la);
-        for (uint32_t w = lane; w < sizeof(LaConst) / 4u; w += 32u) dst[w] = ld_relaxed_sys_u32(src + w);
+    uint64_t* la64 = reinterpret_cast<uint64_t*>(la);
+    LaMail* dmail = ap.la_dmail + (next % kLaTopRing);  // the copy in device memory that CTA 0 publishes
+    constexpr uint32_t kWords = sizeof(LaConst) / 8u;
+    uint64_t tag = 0, geom = 0;
+    // ONE CTA per launch -- the first whose walker gets here -- reads the host-mapped ring: every load is a PCIe round
+    // trip, and 148 CTAs doing so cost 0.4 ms per launch (measured).  The claim word only ever grows.
+    uint32_t fetcher = 0;
+    if (lane == 0) fetcher = atomicMax(reinterpret_cast<unsigned long long*>(&dmail->claim), (unsigned long long)next) < next ? 1u : 0u;
+    fetcher = __shfl_sync(0xffffffffu, fetcher, 0);
+    if (fetcher) {
+        // under a seqlock -- tag, payload, tag again: the host writes 0, payload, tag, and may be re-using the
+        // entry for launch next + 64 -- and republishes the entry in device memory for the other CTAs.
+        const LaMail* mail = ap.la_mail + (next % kLaMailRing);
+        if (lane == 0) {
+            tag = ld_acquire_sys_u64(&mail->tag);
+            geom = tag == next ? ld_relaxed_sys_u64(&mail->geom) : 0ull;
+        }
+        tag = __shfl_sync(0xffffffffu, tag, 0);
+        geom = __shfl_sync(0xffffffffu, geom, 0);
+        if (tag != next) return true;                // not there (no query is queued behind this one) or overwritten
+        const uint64_t* src = reinterpret_cast<const uint64_t*>(&mail->c);
+        for (uint32_t w = lane; w < kWords; w += 32u) la64[w] = ld_relaxed_sys_u64(src + w);
+        asm volatile("fence.acq_rel.sys;" ::: "memory");
+        __syncwarp();
+        uint64_t tag2 = lane == 0 ? ld_acquire_sys_u64(&mail->tag) : 0ull;
+        tag2 = __shfl_sync(0xffffffffu, tag2, 0);
+        if (tag2 != next) return true;               // torn read: give up
+        // device copy, itself under a seqlock (a later launch's CTA 0 may re-use the entry while a straggler reads it)
+        if (lane == 0) st_relaxed_gpu_u64(&dmail->tag, 0ull);
+        __threadfence();
+        __syncwarp();
+        __threadfence();
+        uint64_t* dst = reinterpret_cast<uint64_t*>(&dmail->c);
+        for (uint32_t w = lane; w < kWords; w += 32u) st_relaxed_gpu_u64(dst + w, la64[w]);
+        if (lane == 0) st_relaxed_gpu_u64(&dmail->geom, geom);
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) st_release_gpu_u64(&dmail->tag, next);
+        __syncwarp();
+    } else {
+        for (uint32_t p = 0; p < polls; p++) {
+            if (lane == 0) tag = ld_acquire_gpu_u64(&dmail->tag);
+            tag = __shfl_sync(0xffffffffu, tag, 0);
+            if (tag >= next) break;
+            if (p + 1u < polls) __nanosleep(200);
+        }
+        if (tag != next) return true;                // the fetcher found nothing, or has not got there in time
+        const uint64_t* src = reinterpret_cast<const uint64_t*>(&dmail->c);
+        for (uint32_t w = lane; w < kWords; w += 32u) la64[w] = ld_relaxed_gpu_u64(src + w);
+        if (lane == 0) geom = ld_relaxed_gpu_u64(&dmail->geom);
+        __threadfence();
+        __syncwarp();
+        uint64_t tag2 = lane == 0 ? ld_acquire_gpu_u64(&dmail->tag) : 0ull;
+        tag2 = __shfl_sync(0xffffffffu, tag2, 0);
+        geom = __shfl_sync(0xffffffffu, geom, 0);
+        if (tag2 != next) return true;               // torn read: give up
     }
+    if (geom != ap.la_geom) return true;             // the next launch has another shape: its CTAs walk their own tops
     __syncwarp();
-    asm volatile("fence.acq_rel.sys;" ::: "memory");
-    uint64_t tag2 = lane == 0 ? ld_acquire_sys_u64(&mail->tag) : 0ull;
-    tag2 = __shfl_sync(0xffffffffu, tag2, 0);
-    if (tag2 != next) return true;               // torn read: give up
     const uint32_t dyn_base = smem_addr(g_smem2);
     const TaskIter ti(reinterpret_cast<const uint32_t*>(g_smem2 + kOffTasks));
     TaskShape ts;
@@ -706,18 +780,24 @@ __device__ __noinline__ bool lookahead_next_top(const AnswerPlan& ap, uint32_t t
     const uint4* fs = tt.Lh == tt.Ls ? &path_s[tt.Ls] : hb_s[tt.Lh & 1u];
     const uint8_t* ft = tt.Lh == tt.Ls ? &path_t[tt.Ls] : hb_t[tt.Lh & 1u];
     const uint32_t n = nodes_at(tt.L, tt.a, tt.m, tt.Lh);
+    // The entry is written under a seqlock (ready = 0, nodes, ready = next): with small grids or several streams a launch
+    // four further on can be here while a CTA of an earlier one is still copying the entry's previous contents.
     LaTop* out = ap.la_tops + (next % kLaTopRing) * gridDim.x + blockIdx.x;
+    if (lane == 0) st_relaxed_gpu_u64(&out->ready, 0ull);
+    __threadfence();
+    __syncwarp();
+    __threadfence();
     for (uint32_t j = lane; j < n; j += 32u) {
-        out->seed[j] = fs[j];
-        out->t[j] = ft[j];
+        __stcg(&out->seed[j], fs[j]);
+        __stcg(&out->t[j], ft[j]);
+    }
+    if (lane == 0) {
+        __stcg(&out->n, n);
+        __stcg(&out->lh, tt.Lh);
     }
     __threadfence();
     __syncwarp();
-    if (lane == 0) {
-        out->n = n;
-        out->lh = tt.Lh;
-        st_release_gpu_u64(&out->ready, next);
-    }
+    if (lane == 0) st_release_gpu_u64(&out->ready, next);
     __syncwarp();
     return true;
 }
@@ -742,12 +822,6 @@ __device__ __forceinline__ void consume_slices(const QueryConst& qc, const Answe
     for (int cb = 0; cb < NCB; cb++) acc[cb] = make_uint4(0, 0, 0, 0);
     long long c_wait = 0;
     const long long c_in = PIRB_AP_DBG(ap) ? clock64() : 0;
-    // Look-ahead (DUAL warp of a CTA with one task, ap.la_mail set): before the first slice arrives the scan warps
-    // idle anyway, so that is when the next launch's top is walked; if its mail is not there yet, poll again after
-    // 16, 64 and 256 scan units.
-    bool la_todo = DUAL && ap.la_mail != nullptr && ti.n == 1u;
-    uint32_t la_units = 0, la_next = 16u;
-    if (la_todo) la_todo = !lookahead_next_top(ap, qc.num_bits - 1u);
     // DUAL: this scan warp also walks the tops of the tasks ahead (TopWalker), before anything else whenever a
     // hand-over buffer is free -- the tree warps will wait for it at the next task boundary, the scan has slack.
     while (true) {
@@ -765,10 +839,6 @@ __device__ __forceinline__ void consume_slices(const QueryConst& qc, const Answe
             gs1 += 1u << ti.slices_log(ti.pos++);
         }
         if (!have) break;
-        if (la_todo && ++la_units == la_next) {
-            la_next = la_next >= 256u ? 0xffffffffu : la_next * 4u;
-            la_todo = !lookahead_next_top(ap, qc.num_bits - 1u);
-        }
         const uint32_t slot = gsl & (kRing - 1u), par = (gsl / kRing) & 1u;
         const long long cw0 = (PIRB_AP_DBG(ap) && warp_in_cta == kTreeWarps) ? clock64() : 0;
         if (DUAL) {
@@ -858,27 +928,43 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
         const uint32_t Ls = single_node_levels(L, a, m);
         uint32_t l_bfs = Ls;  // first breadth-first level the tree warps expand themselves
         bool la_hit = false;
+#ifndef PIRB_NO_LA_CODE
         if (it == 0u && n_tasks == 1u && ap.la_tops != nullptr) {
-            // has the launch before this one left this task's top for us (look-ahead)?
+            // Has the launch before this one left this task's top for us (look-ahead)?  Seqlock read: the sequence number,
+            // the nodes (into registers), the sequence number again; anything but two matches and we walk the top ourselves.
             const uint32_t Lh = hand_level(L, a, m, Ls);
+            const uint32_t n_h = nodes_at(L, a, m, Lh);
             volatile uint32_t* flag = reinterpret_cast<volatile uint32_t*>(g_smem2 + kOffPathT + 72);
             const LaTop* in = ap.la_tops + (ap.la_seq % kLaTopRing) * gridDim.x + blockIdx.x;
             if (tid == 0) {
                 bool ok = ld_acquire_gpu_u64(&in->ready) == ap.la_seq;
-                if (ok) ok = __ldcg(&in->lh) == Lh && __ldcg(&in->n) == nodes_at(L, a, m, Lh);
+                if (ok) ok = __ldcg(&in->lh) == Lh && __ldcg(&in->n) == n_h;
                 *flag = ok ? 1u : 0u;
             }
             bar_sync(BAR_TREE, kTreeThreads);
-            la_hit = *flag != 0u;
-            if (la_hit) {
-                if (tid < nodes_at(L, a, m, Lh)) {
-                    bfs_s[(Lh & 1u) * kTreeThreads + tid] = __ldcg(&in->seed[tid]);
-                    bfs_t[(Lh & 1u) * kTreeThreads + tid] = __ldcg(&in->t[tid]);
+            if (*flag != 0u) {
+                uint4 sv = make_uint4(0, 0, 0, 0);
+                uint8_t tv = 0;
+                if (tid < n_h) {
+                    sv = __ldcg(&in->seed[tid]);
+                    tv = __ldcg(&in->t[tid]);
+                }
+                __threadfence();
+                bar_sync(BAR_TREE, kTreeThreads);  // (every thread's loads are done; flag has been read by all)
+                if (tid == 0) *flag = ld_acquire_gpu_u64(&in->ready) == ap.la_seq ? 1u : 0u;
+                bar_sync(BAR_TREE, kTreeThreads);
+                la_hit = *flag != 0u;
+                if (la_hit) {
+                    if (tid < n_h) {
+                        bfs_s[(Lh & 1u) * kTreeThreads + tid] = sv;
+                        bfs_t[(Lh & 1u) * kTreeThreads + tid] = tv;
+                    }
+                    l_bfs = Lh;
                 }
                 bar_sync(BAR_TREE, kTreeThreads);
-                l_bfs = Lh;
             }
         }
+#endif
         if (la_hit) {
             // (nothing to walk)
         } else if (ap.top_warp && it > 0u) {
@@ -1147,6 +1233,13 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
         // the last scan warp doubles as the top walker
         const bool dual = ap.top_warp != 0u && threadIdx.x >= kAnswerThreads - 32;
         if constexpr (NCB != 0) {
+            // Look-ahead (the walker warp of a CTA with one task, ap.la_mail set): until the first slice arrives the scan
+            // warps idle anyway, so that is when the next launch's top is walked.  One attempt per launch: under load the
+            // next launch's mail has been waiting since long before this one started.
+#ifndef PIRB_NO_LA_CODE
+            if (dual && ap.la_mail != nullptr && *reinterpret_cast<const uint32_t*>(g_smem2 + kOffTasks) == 1u)
+                lookahead_next_top(ap, qc.num_bits - 1u, 48u);
+#endif
             consume_slices<NCB>(qc, ap, threadIdx.x >> 5, dual);
         } else if (dual) {
             const uint32_t n_tasks = *reinterpret_cast<const uint32_t*>(g_smem2 + kOffTasks);
@@ -1205,7 +1298,7 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
 }
 
 bool answer_kernel_supports(uint64_t row_bytes, uint32_t D) {
-    if (row_bytes < 16 || row_bytes > kMaxRowBytes || (row_bytes & (row_bytes - 1))) return false;
+    if (row_bytes < 16 || row_bytes > kMaxRowBytes || (row_bytes & 15)) return false;  // any multiple of 16 up to 4 KB
     return D <= (uint32_t)kV2MaxDepth;
 }
 
@@ -1274,9 +1367,9 @@ cudaError_t launch_answer(const QueryConst& qc, const AnswerPlan& ap, const uint
         PIRB_LAUNCH(0);
     else if (ap.row_bytes <= 512)
         PIRB_LAUNCH(1);
-    else if (ap.row_bytes == 1024)
+    else if (ap.row_bytes <= 1024)
         PIRB_LAUNCH(2);
-    else if (ap.row_bytes == 2048)
+    else if (ap.row_bytes <= 2048)
         PIRB_LAUNCH(4);
     else
         PIRB_LAUNCH(8);

@@ -272,6 +272,7 @@ struct pir_db {
     LaMail* h_mail = nullptr;
     const LaMail* h_mail_dev = nullptr;
     LaTop* d_tops = nullptr;
+    LaMail* d_mail = nullptr;
     uint64_t la_seq = 0;
     uint64_t h_out_cap = 0;
     // cached work split of the answer kernel for the last (num_bits, shard rows) seen
@@ -515,6 +516,8 @@ extern "C" int pir_db_create(int device, uint64_t db_size, uint32_t slot_bytes, 
     const size_t tops_bytes = (size_t)kLaTopRing * (size_t)ctx->num_sms * sizeof(LaTop);
     if (e == cudaSuccess) e = cudaMalloc(&db->d_tops, tops_bytes);
     if (e == cudaSuccess) e = cudaMemsetAsync(db->d_tops, 0, tops_bytes, db->stream);
+    if (e == cudaSuccess) e = cudaMalloc(&db->d_mail, kLaTopRing * sizeof(LaMail));
+    if (e == cudaSuccess) e = cudaMemsetAsync(db->d_mail, 0, kLaTopRing * sizeof(LaMail), db->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(db->stream);
     if (e != cudaSuccess) {
         int code = e == cudaErrorMemoryAllocation ? PIR_ERR_OOM : PIR_ERR_CUDA;
@@ -541,6 +544,7 @@ extern "C" int pir_db_destroy(pir_db* db) {
     if (db->d_acc) cudaFree(db->d_acc);
     if (db->acc_ev) cudaEventDestroy(db->acc_ev);
     if (db->d_tops) cudaFree(db->d_tops);
+    if (db->d_mail) cudaFree(db->d_mail);
     if (db->h_mail) cudaFreeHost(db->h_mail);
     for (int k = 0; k < 2; k++)
         if (db->side[k]) cudaStreamDestroy(db->side[k]);
@@ -742,6 +746,27 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
         if (!db->d_keywords) return fail(PIR_ERR_BAD_ARG, "keyword query on a database without keywords (pir_db_set_keywords)");
         if (g.first_row < db->slot_begin || g.first_row + g.n_rows > db->slot_begin + db->slot_count)
             return fail(PIR_ERR_BAD_ARG, "keyword queries with group_size > 1 need an unsharded handle");
+        // keyword queries need group size 1 on a shard (checked above), so row r of the shard is slot slot_begin + r
+        const uint8_t* rows0 = db->d_slots + (g.first_row * g.W - db->slot_begin) * (uint64_t)db->pitch;
+        if (!db->tune.keyword_v1 && !db->tune.force_unfused && keyword_fused_supports(g.row_bytes)) {
+            // one kernel: prefix-sharing walk with the row XOR fused in (no byte-per-row bit vector through HBM)
+            cudaEvent_t e0 = nullptr, e1 = nullptr;
+            if (db->timing) {
+                if (db->ev_used == db->ev_pool.size()) {
+                    CU(cudaEventCreate(&e0));
+                    CU(cudaEventCreate(&e1));
+                    db->ev_pool.emplace_back(e0, e1);
+                }
+                e0 = db->ev_pool[db->ev_used].first;
+                e1 = db->ev_pool[db->ev_used].second;
+                db->ev_used++;
+                CU(cudaEventRecord(e0, st));
+            }
+            CU(launch_keyword_walk(qc, db->d_keywords + (g.first_row - db->slot_begin), 0, g.n_rows, nullptr, nullptr, ctx.d_t0,
+                                   ctx.smem_base, ctx.num_sms, st, rows0, g.row_bytes, (uint32_t*)d_out));
+            if (e1) CU(cudaEventRecord(e1, st));
+            return PIR_OK;
+        }
         if ((rc = ensure_bits(db, g.n_rows))) return rc;
         if (db->tune.keyword_v1)
             CU(launch_eval_points(qc, db->d_keywords + (g.first_row - db->slot_begin), 0, g.n_rows, nullptr,
@@ -749,7 +774,7 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
         else
             CU(launch_keyword_walk(qc, db->d_keywords + (g.first_row - db->slot_begin), 0, g.n_rows, nullptr,
                                    db->d_bits, ctx.d_t0, ctx.smem_base, ctx.num_sms, st));
-        CU(launch_scan_bytes(db->d_slots, g.row_bytes, g.n_rows, db->d_bits, (uint32_t*)d_out, ctx.num_sms, st));
+        CU(launch_scan_bytes(rows0, g.row_bytes, g.n_rows, db->d_bits, (uint32_t*)d_out, ctx.num_sms, st));
         return PIR_OK;
     }
     if (!db->tune.kernel_v1 && answer_kernel_supports(g.row_bytes, 0)) {
@@ -802,6 +827,7 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
             ap.la_seq = seq;
             ap.la_geom = hsh;
             ap.la_mail = db->h_mail_dev;
+            ap.la_dmail = db->d_mail;
             ap.la_tops = db->d_tops;
         }
 #ifdef PIRB_DEV

@@ -49,8 +49,9 @@ struct LaConst {                       // what a top walk needs of QueryConst; s
     uint32_t t_init, pad;
 };
 struct LaMail {
-    uint64_t tag;    // sequence number of the launch this entry belongs to; 0 while the host is writing it
+    uint64_t tag;    // sequence number of the launch this entry belongs to; 0 while it is being written
     uint64_t geom;   // hash of shard geometry and work split: the top is only valid for an identical launch shape
+    uint64_t claim;  // device copy only: highest sequence number some CTA has set out to fetch from the host ring
     LaConst c;
 };
 struct LaTop {       // one per (ring entry, CTA)
@@ -95,6 +96,7 @@ struct AnswerPlan {
     // the host-mapped mail ring [kLaMailRing] and the tops ring [kLaTopRing][gridDim.x] in device memory
     uint64_t la_seq, la_geom;
     const LaMail* la_mail;
+    LaMail* la_dmail;     // [kLaTopRing] in device memory: CTA 0 republishes the next launch's mail here for the other CTAs
     LaTop* la_tops;
 };
 
@@ -149,8 +151,11 @@ cudaError_t launch_eval_points(const QueryConst& qc, const uint64_t* xs, uint64_
                                cudaStream_t st);
 // the same with prefix sharing between consecutive points (keyword_kernel.cu): the keyword path
 cudaError_t configure_keyword_kernel();
+// db != nullptr: the row XOR is fused into the walk (rows of a multiple of 16 up to 512 bytes, keyword_fused_supports)
+bool keyword_fused_supports(uint64_t row_bytes);
 cudaError_t launch_keyword_walk(const QueryConst& qc, const uint64_t* xs, uint64_t x_first, uint64_t n, int64_t* values,
-                                uint8_t* bits, const uint32_t* d_t0, uint32_t smem_base, int num_sms, cudaStream_t st);
+                                uint8_t* bits, const uint32_t* d_t0, uint32_t smem_base, int num_sms, cudaStream_t st,
+                                const uint8_t* db = nullptr, uint64_t row_bytes = 0, uint32_t* out = nullptr);
 // masked XOR of rows from a byte-per-row bit vector (any row_bytes multiple of 16)
 cudaError_t launch_scan_bytes(const uint8_t* db, uint64_t row_bytes, uint64_t n_rows, const uint8_t* bits,
                               uint32_t* out, int num_sms, cudaStream_t st);

@@ -398,3 +398,53 @@ def test_back_to_back_launches_with_lookahead_and_overlap(gpu_lib, log_rows, slo
             # the host call (one launch + sync per query) follows the same path one query at a time
             for k in (0, 1, 39):
                 assert np.array_equal(h.answer(keys[k][1]), want[k])
+
+
+@pytest.mark.parametrize("slot_bytes,W", [(16, 1), (24, 1), (100, 1), (256, 1), (512, 1), (1024, 1), (16, 5)])
+def test_keyword_answer_fused_walk_for_every_row_size(gpu_lib, slot_bytes, W):
+    """The keyword answer path walks and XORs in one kernel for rows up to 512 bytes (any multiple of 16: 32/c rows per
+    warp load) and falls back to walk + scan for wider rows; both, and the per-row kernel, must give the oracle's bytes."""
+    db_size = 20000
+    rng = np.random.default_rng(slot_bytes + W)
+    data = rng.integers(0, 256, size=(db_size, slot_bytes), dtype=np.uint8)
+    rows = db_size // W
+    kws = np.sort(rng.choice(1 << 32, size=rows, replace=False).astype(np.uint64))
+    target = rows // 3
+    (o0, o1), (q0, q1) = make_queries(70 + slot_bytes, db_size, W, target, is_keyword=True, keyword=int(kws[target]))
+    kw_all = np.zeros(db_size, dtype=np.uint64)
+    kw_all[:rows] = kws      # Database.Keywords is indexed by row (db.go:132-135); one entry per slot is what the handle takes
+    with Handle(db_size, slot_bytes) as h:
+        h.upload(data)
+        h.set_keywords(kw_all)
+        w0 = oracle.answer(o0, data, db_size, slot_bytes, keywords=kw_all)
+        w1 = oracle.answer(o1, data, db_size, slot_bytes, keywords=kw_all)
+        for opts in ({}, {"force_unfused": 1}, {"keyword_v1": 1}):
+            for name in ("force_unfused", "keyword_v1"):
+                h.set_option(name, opts.get(name, 0))
+            a0, a1 = h.answer(q0), h.answer(q1)
+            assert np.array_equal(a0, w0) and np.array_equal(a1, w1), opts
+            assert np.array_equal(a0 ^ a1, data[target * W:(target + 1) * W].reshape(-1))
+
+
+@pytest.mark.parametrize("slot_bytes,W", [(48, 1), (80, 1), (100, 3), (176, 3), (1008, 1), (336, 9), (4096, 1), (24, 7), (8, 3)])
+def test_any_row_size_takes_the_warp_specialised_kernel(gpu_lib, slot_bytes, W):
+    """Rows of any multiple of 16 bytes up to 4 KB (slot pitch x group size) run the warp-specialised answer kernel:
+    c chunks per row, the largest power of two <= 32 / c rows per warp load, the last 512-byte column block of a wide
+    row partly filled.  Bytes must equal the oracle's and the older two-launch path's, single queries and batches."""
+    db_size = 60000
+    data = oracle.synth_fill(3, 0, db_size, slot_bytes)
+    rows = db_size // W
+    with Handle(db_size, slot_bytes) as h:
+        h.fill(3)
+        for trial, idx in enumerate((0, rows // 2 + 1, rows - 1)):
+            (o0, o1), (q0, q1) = make_queries(600 + trial, db_size, W, idx)
+            w0 = oracle.answer(o0, data, db_size, slot_bytes, use_tree=True)
+            w1 = oracle.answer(o1, data, db_size, slot_bytes, use_tree=True)
+            h.set_option("kernel_v1", 0)
+            a0, a1 = h.answer(q0), h.answer(q1)
+            assert np.array_equal(a0, w0) and np.array_equal(a1, w1), idx
+            assert np.array_equal(a0 ^ a1, data[idx * W:(idx + 1) * W].reshape(-1))
+            both = h.answer_batch([q0, q1, q0, q1, q0])
+            assert np.array_equal(both[3], w1) and np.array_equal(both[4], w0)
+            h.set_option("kernel_v1", 1)
+            assert np.array_equal(h.answer(q0), w0)

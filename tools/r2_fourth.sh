@@ -1,0 +1,12 @@
+#!/bin/bash
+mkdir -p gpurun_out
+( time timeout 900 python -m pytest tests -m gpu -q ) > gpurun_out/r2d_gpu_tests.log 2>&1; tail -6 gpurun_out/r2d_gpu_tests.log; grep -E "^FAILED|^E  " gpurun_out/r2d_gpu_tests.log | head -20
+: > gpurun_out/variant_shards.log
+VARIANTS="pre_la cur" bash tools/variant_shards.sh
+python bench.py > gpurun_out/r2d_bench.json 2> gpurun_out/r2d_bench.err; echo bench rc=$?; tail -3 gpurun_out/r2d_bench.err
+python - <<'PY'
+import json
+d=json.load(open('gpurun_out/r2d_bench.json')); r=d['roofline']
+print('value',round(d['value']),'ms',round(d['ms_per_step'],4),'e2e',round(d['e2e']['value']),'iso',round(r['kernel_ms_isolated'],4),'aes',round(r['lookup']['aes_only_ms'],4))
+for o in d['other_configs']: print(o['config'], round(o['ms_per_step'],4), round(o['value'],1), o['parity_checked'])
+PY

@@ -14,6 +14,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from pir_b200 import _capi  # noqa: E402
 
+if os.environ.get("VARIANT_SO"):     # A/B of library builds (tools/variant_shards.sh); a tool-side switch, not the product's
+    _capi.LIB_PATH = os.environ["VARIANT_SO"]
 L = _capi.lib()
 n, S = 1 << int(os.environ.get("LOG_ROWS", "24")), int(os.environ.get("SLOT", "256"))
 nb = L.pir_num_bits_for(n, 1, 0)
@@ -35,8 +37,8 @@ for frac in (1, 2, 4, 8):
     d_out = torch.zeros((2 * NQ, S), dtype=torch.uint8, device="cuda")
     res = {}
     for la, ser in ((0, 0), (1, 0), (0, 1), (1, 1)):
-        _capi.check(L.pir_db_set_option(h, b"no_lookahead", la))
-        _capi.check(L.pir_db_set_option(h, b"serial_launch", ser))
+        L.pir_db_set_option(h, b"no_lookahead", la)     # (a variant built before an option existed just ignores it)
+        L.pir_db_set_option(h, b"serial_launch", ser)
         best = 1e9
         for rep in range(3):
             torch.cuda.synchronize()
