@@ -1032,6 +1032,8 @@ __device__ __forceinline__ void tree_role(const QueryConst& qc, const AnswerPlan
                                rv ? rs : nullptr, rv ? &bfs_t[dst + ri] : nullptr);
                 }
             } else if (tid < n) {
+                // (one node per thread with the rolled rounds: ~4k cycles per level.  The unrolled AES of the depth-first
+                //  loop as an out-of-line copy was measured slower, profiles/r2_shard_probe_variants.txt "widebfs")
                 const uint4 sv = bfs_s[src + tid];
                 const uint32_t sw[4] = {sv.x, sv.y, sv.z, sv.w};
                 Children ch;
