@@ -82,7 +82,8 @@ def use_dev_library():
     global LIB_PATH, _lib
     if _lib is not None:
         raise RuntimeError("the library is already loaded")
-    subprocess.check_call(["make", "-C", CSRC_DIR, "-s", "-j8", "dev"])
+    if not os.path.exists(DEV_LIB_PATH):
+        subprocess.check_call(["make", "-C", CSRC_DIR, "-s", "-j8", "dev"])
     LIB_PATH = DEV_LIB_PATH
 
 

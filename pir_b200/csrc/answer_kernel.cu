@@ -672,6 +672,7 @@ __device__ __forceinline__ void st_relaxed_gpu_u64(uint64_t* p, uint64_t v) {
     asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 static_assert(sizeof(LaConst) % 8 == 0, "LaConst is copied in 64-bit words");
+constexpr uint64_t kLaNone = 1ull << 63;  // device copy of the mail: "the fetcher found no mail for this sequence number"
 
 // `polls`: how often a CTA other than the fetcher looks for the device copy of the mail before it goes on to scan.
 __device__ __noinline__ bool lookahead_next_top(const AnswerPlan& ap, uint32_t top_bits, uint32_t polls) {
@@ -697,7 +698,11 @@ __device__ __noinline__ bool lookahead_next_top(const AnswerPlan& ap, uint32_t t
         }
         tag = __shfl_sync(0xffffffffu, tag, 0);
         geom = __shfl_sync(0xffffffffu, geom, 0);
-        if (tag != next) return true;                // not there (no query is queued behind this one) or overwritten
+        if (tag != next) {
+            // not there (no query is queued behind this one) or overwritten: tell the other CTAs so that they stop looking
+            if (lane == 0) st_release_gpu_u64(&dmail->tag, next | kLaNone);
+            return true;
+        }
         const uint64_t* src = reinterpret_cast<const uint64_t*>(&mail->c);
         for (uint32_t w = lane; w < kWords; w += 32u) la64[w] = ld_relaxed_sys_u64(src + w);
         asm volatile("fence.acq_rel.sys;" ::: "memory");
@@ -721,8 +726,8 @@ __device__ __noinline__ bool lookahead_next_top(const AnswerPlan& ap, uint32_t t
         for (uint32_t p = 0; p < polls; p++) {
             if (lane == 0) tag = ld_acquire_gpu_u64(&dmail->tag);
             tag = __shfl_sync(0xffffffffu, tag, 0);
-            if (tag >= next) break;
-            if (p + 1u < polls) __nanosleep(200);
+            if ((tag & ~kLaNone) >= next) break;
+            if (p + 1u < polls) __nanosleep(300);
         }
         if (tag != next) return true;                // the fetcher found nothing, or has not got there in time
         const uint64_t* src = reinterpret_cast<const uint64_t*>(&dmail->c);
@@ -1240,7 +1245,7 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
             // next launch's mail has been waiting since long before this one started.
 #ifndef PIRB_NO_LA_CODE
             if (dual && ap.la_mail != nullptr && *reinterpret_cast<const uint32_t*>(g_smem2 + kOffTasks) == 1u)
-                lookahead_next_top(ap, qc.num_bits - 1u, 48u);
+                lookahead_next_top(ap, qc.num_bits - 1u, 16u);
 #endif
             consume_slices<NCB>(qc, ap, threadIdx.x >> 5, dual);
         } else if (dual) {

@@ -733,14 +733,15 @@ int query_geom(const pir_db* db, const pir_query* q, QueryGeom* g) {
 // on every other path the caller launches the signalling kernel.
 int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* d_out, cudaStream_t st,
                    bool zero_first = true, uint32_t* arrivals = nullptr, bool* signalled = nullptr, bool throughput = false,
-                   uint32_t* final_out = nullptr) {
+                   uint32_t* final_out = nullptr, const QueryConst* prebuilt = nullptr) {
     // every kernel below XOR-accumulates into d_out (atomics), so a caller that combines several shards
     // into one buffer passes zero_first = false and zeroes it once itself
     if (zero_first) CU(cudaMemsetAsync(d_out, 0, g.row_bytes, st));
     if (g.n_rows == 0) return PIR_OK;
-    QueryConst qc;
-    int rc = build_query_const(q, g.nb, &qc);
-    if (rc) return rc;
+    QueryConst qc_local;
+    int rc = PIR_OK;
+    if (!prebuilt && (rc = build_query_const(q, g.nb, &qc_local))) return rc;
+    const QueryConst& qc = prebuilt ? *prebuilt : qc_local;  // (a multi-shard server marshals every key once, not once per shard)
     const DeviceCtx& ctx = *db->ctx;
     if (q->is_keyword) {
         if (!db->d_keywords) return fail(PIR_ERR_BAD_ARG, "keyword query on a database without keywords (pir_db_set_keywords)");
@@ -961,14 +962,18 @@ bool batch_uses_bits_path(const pir_db* db, const pir_query* qs, uint32_t n, con
 // is read), phase 2 streams the shard once and folds every row into the accumulators of the queries that
 // selected it (batch_scan.cu).  d_out: n pitched answers, XOR-accumulated (zeroed here if zero_first).
 int enqueue_batch_bits(pir_db* db, const pir_query* qs, uint32_t n, const QueryGeom& g, uint8_t* d_out, cudaStream_t st,
-                       bool zero_first = true) {
+                       bool zero_first = true, const QueryConst* prebuilt = nullptr) {
     // Every key is validated and marshalled BEFORE anything is enqueued: a bad key at position k must not leave the
     // kernels of queries 0..k-1 running on the side streams behind the caller's back.
-    std::vector<QueryConst> qcs(n);
-    for (uint32_t i = 0; i < n; i++) {
-        int rc = build_query_const(&qs[i], g.nb, &qcs[i]);
-        if (rc) return rc;
+    std::vector<QueryConst> qcs_local;
+    if (!prebuilt) {
+        qcs_local.resize(n);
+        for (uint32_t i = 0; i < n; i++) {
+            int rc = build_query_const(&qs[i], g.nb, &qcs_local[i]);
+            if (rc) return rc;
+        }
     }
+    const QueryConst* qcs = prebuilt ? prebuilt : qcs_local.data();
     const DeviceCtx& ctx = *db->ctx;
     const uint64_t wpq = (((g.n_rows + 31) >> 5) + 1 + 3) & ~3ull;  // +1: a slice may spill into the next word
     if ((uint64_t)n * wpq > db->bitmat_cap) {
@@ -1506,6 +1511,7 @@ struct pir_combine {
     uint8_t* base = nullptr;  // device pointer valid in this process
     cudaStream_t stream = nullptr;  // owner: reset / wait / read
     uint8_t* h_buf = nullptr;       // owner: pinned staging of one slot + the timeout flag
+    uint8_t* h_buf_dev = nullptr;   // the same buffer as the device sees it (mapped), or null
     int clock_khz = 0;
     std::mutex mu;
     uint32_t* arrivals(uint32_t slot) const { return (uint32_t*)(base + (size_t)n_slots * stride) + slot; }
@@ -1538,6 +1544,12 @@ extern "C" int pir_combine_create(int device, uint32_t n_slots, size_t slot_stri
     if (e == cudaSuccess) e = cudaDeviceSynchronize();  // (the slots are used from non-blocking streams and other processes)
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaMallocHost(&c->h_buf, slot_stride + 16);
+    if (e == cudaSuccess) {
+        memset(c->h_buf, 0, slot_stride + 16);
+        void* dp = nullptr;
+        if (cudaHostGetDevicePointer(&dp, c->h_buf, 0) == cudaSuccess) c->h_buf_dev = (uint8_t*)dp;
+        else cudaGetLastError();
+    }
     c->clock_khz = ctx->clock_khz;
     if (e != cudaSuccess) {
         int code = e == cudaErrorMemoryAllocation ? PIR_ERR_OOM : PIR_ERR_CUDA;
@@ -1693,9 +1705,19 @@ extern "C" int pir_combine_wait_read_reset(pir_combine* c, uint32_t slot, uint32
     std::lock_guard<std::mutex> lk(c->mu);
     DeviceGuard g(c->device);
     const uint64_t cycles = (uint64_t)(c->clock_khz > 0 ? c->clock_khz : 1000000) * (timeout_ms ? timeout_ms : 1);
+    uint32_t* h_flag = (uint32_t*)(c->h_buf + c->stride);
+    if (c->h_buf_dev) {
+        // one launch: wait for the arrivals, move the answer to the mapped pinned buffer, zero slot and counter
+        CU(launch_wait_read_reset(c->arrivals(slot), expected, cycles, (uint32_t*)(c->base + (size_t)slot * c->stride),
+                                  (uint32_t*)c->h_buf_dev, (uint32_t*)(c->h_buf_dev + c->stride), (uint32_t)(c->stride / 4), c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        if (*h_flag) return fail(PIR_ERR_CUDA, "timed out after %u ms waiting for %u shard arrivals at combine slot %u", timeout_ms,
+                                 expected, slot);
+        memcpy(out, c->h_buf, out_len);
+        return PIR_OK;
+    }
     CU(launch_wait_arrivals(c->arrivals(slot), expected, cycles, c->timeout_flag(), c->stream));
     CU(cudaMemcpyAsync(c->h_buf, c->base + (size_t)slot * c->stride, out_len, cudaMemcpyDeviceToHost, c->stream));
-    uint32_t* h_flag = (uint32_t*)(c->h_buf + c->stride);
     CU(cudaMemcpyAsync(h_flag, c->timeout_flag(), 4, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaMemsetAsync(c->base + (size_t)slot * c->stride, 0, c->stride, c->stream));
     CU(cudaMemsetAsync(c->arrivals(slot), 0, 4, c->stream));
@@ -1898,6 +1920,7 @@ extern "C" int pir_server_answer_batch(pir_server* s, const pir_query* qs, uint3
     // (a group size that does not divide that shard's first slot, a bad key) must not leave the kernels of the shards
     // before it XOR-ing into the accumulator while the caller already sees a failure.
     std::vector<QueryGeom> geoms(s->shards.size());
+    std::vector<QueryConst> qcs(n_queries);  // marshalled once, shared by all shards (the key material is the same)
     for (size_t i = 0; i < s->shards.size(); i++) {
         for (uint32_t k = 0; k < n_queries; k++) {
             if (qs[k].group_size != W || qs[k].is_keyword != qs[0].is_keyword)
@@ -1905,10 +1928,8 @@ extern "C" int pir_server_answer_batch(pir_server* s, const pir_query* qs, uint3
             QueryGeom geom;
             if ((rc = query_geom(s->shards[i], &qs[k], &geom))) return rc;
             if (k == 0) geoms[i] = geom;
-            if (i == 0) {
-                QueryConst qc;
-                if ((rc = build_query_const(&qs[k], geom.nb, &qc))) return rc;
-            }
+            if (i == 0 && (rc = build_query_const(&qs[k], geom.nb, &qcs[k]))) return rc;
+            if (geom.nb != geoms[0].nb) return fail(PIR_ERR_BAD_ARG, "shards disagree on the domain size");
         }
         if (qs[0].is_keyword && geoms[i].n_rows && !s->shards[i]->d_keywords)
             return fail(PIR_ERR_BAD_ARG, "keyword query on a database without keywords (pir_server_set_keywords)");
@@ -1930,10 +1951,11 @@ extern "C" int pir_server_answer_batch(pir_server* s, const pir_query* qs, uint3
             int r = PIR_OK;
             if (batch_uses_bits_path(db, qs, n_queries, geoms[i])) {
                 // two-phase batch per shard; its scan kernel XORs into the shared accumulator like the fused one
-                r = enqueue_batch_bits(db, qs, n_queries, geoms[i], s->d_acc, db->stream, /*zero_first=*/false);
+                r = enqueue_batch_bits(db, qs, n_queries, geoms[i], s->d_acc, db->stream, /*zero_first=*/false, qcs.data());
             } else {
                 for (uint32_t k = 0; k < n_queries && r == PIR_OK; k++)
-                    r = enqueue_answer(db, &qs[k], geoms[i], s->d_acc + (uint64_t)k * row_bytes, db->stream, false);
+                    r = enqueue_answer(db, &qs[k], geoms[i], s->d_acc + (uint64_t)k * row_bytes, db->stream, false, nullptr, nullptr,
+                                       false, nullptr, &qcs[k]);
             }
             return r;
         };

@@ -564,6 +564,43 @@ __global__ void wait_arrivals_kernel(const uint32_t* arrivals, uint32_t expected
     }
 }
 
+// Owner GPU, one launch per query of the end-to-end path: wait (bounded) for the shards' arrivals, move the combined
+// answer to the caller's mapped pinned buffer, and leave slot and counter zeroed for the slot's next query
+// (atomicExch reads and clears in one go).  *h_flag = 1 on a timeout (nothing is moved then).
+__global__ void wait_read_reset_kernel(uint32_t* arrivals, uint32_t expected, uint64_t timeout_cycles, uint32_t* slot,
+                                       uint32_t* h_out, uint32_t* h_flag, uint32_t words) {
+    __shared__ uint32_t ok;
+    if (threadIdx.x == 0) {
+        const long long t0 = clock64();
+        ok = 1u;
+        while (true) {
+            uint32_t v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(arrivals) : "memory");
+            if (v >= expected) break;
+            if ((uint64_t)(clock64() - t0) > timeout_cycles) {
+                ok = 0u;
+                break;
+            }
+            __nanosleep(100);
+        }
+    }
+    __syncthreads();
+    if (ok) {
+        __threadfence_system();
+        for (uint32_t i = threadIdx.x; i < words; i += blockDim.x) h_out[i] = atomicExch(&slot[i], 0u);
+        if (threadIdx.x == 0) *arrivals = 0u;
+    }
+    if (threadIdx.x == 0) *h_flag = ok ? 0u : 1u;
+    __threadfence_system();
+}
+
+cudaError_t launch_wait_read_reset(uint32_t* arrivals, uint32_t expected, uint64_t timeout_cycles, uint32_t* slot, uint32_t* h_out,
+                                   uint32_t* h_flag, uint32_t words, cudaStream_t st) {
+    wait_read_reset_kernel<<<1, 128, 0, st>>>(arrivals, expected, timeout_cycles, slot, h_out, h_flag, words);
+    g_launches++;
+    return cudaGetLastError();
+}
+
 cudaError_t launch_signal_arrival(uint32_t* arrivals, cudaStream_t st) {
     signal_arrival_kernel<<<1, 1, 0, st>>>(arrivals);
     g_launches++;

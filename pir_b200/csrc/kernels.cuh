@@ -181,6 +181,9 @@ cudaError_t launch_unpack_bits(const uint32_t* packed, uint8_t* bytes, uint64_t 
 cudaError_t launch_signal_arrival(uint32_t* arrivals, cudaStream_t st);
 cudaError_t launch_wait_arrivals(const uint32_t* arrivals, uint32_t expected, uint64_t timeout_cycles,
                                  uint32_t* timed_out, cudaStream_t st);
+// wait, move the combined answer to a mapped pinned host buffer, zero slot and counter: one launch
+cudaError_t launch_wait_read_reset(uint32_t* arrivals, uint32_t expected, uint64_t timeout_cycles, uint32_t* slot, uint32_t* h_out,
+                                   uint32_t* h_flag, uint32_t words, cudaStream_t st);
 
 bool batch_scan_geometry(uint64_t row_bytes, uint32_t* tpq, uint32_t* seg_chunks, uint32_t* stage_rows,
                          uint32_t* queries_per_launch);

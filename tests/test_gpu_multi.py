@@ -96,6 +96,31 @@ def test_combine_slots_single_process(gpu_lib):
         comb.close()
 
 
+def test_combine_wait_read_reset_frees_the_slot(gpu_lib):
+    """pir_combine_wait_read_reset: one launch waits for the arrivals, moves the answer to the host and zeroes slot and
+    counter, so the same slot serves the next query at once (the end-to-end loop of bench.py: ring of 4 slots)."""
+    n, S = 1 << 13, 256
+    data = oracle.synth_fill(9, 0, n, S)
+    comb = sharding.Combine(0, 2, S)
+    try:
+        with Handle(n, S, 0, n // 2) as h0, Handle(n, S, n // 2, n // 2) as h1:
+            h0.fill(9)
+            h1.fill(9)
+            for k in range(12):
+                (o0, o1), (q0, q1) = make_queries(300 + k, n, 1, (k * 811) % n)
+                o, q = ((o0, q0), (o1, q1))[k & 1]
+                slot = k & 1
+                comb.accumulate(h0.h, q, slot)
+                comb.accumulate(h1.h, q, slot)
+                got = comb.wait_read_reset(slot, 2, S)
+                assert np.array_equal(got, oracle.answer(o, data, n, S)), k
+            with pytest.raises(_capi.PirError):
+                comb.wait_read_reset(0, 1, S, timeout_ms=20)      # nothing pending: times out, the slot stays clean
+            assert not comb.wait_read(0, 0, S).any() and not comb.wait_read(1, 0, S).any()
+    finally:
+        comb.close()
+
+
 def test_combine_wait_times_out(gpu_lib):
     comb = sharding.Combine(0, 1, 64)
     try:
