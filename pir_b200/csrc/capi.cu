@@ -228,6 +228,7 @@ struct Tuning {
     bool host_copy_path = false;  // pir_answer: memset + kernel + copy instead of the one-launch host path
     bool serial_launch = false;   // no programmatic dependent launch between consecutive answer kernels
     bool no_lookahead = false;    // launches do not walk the next launch's tree top (kernels.cuh LaMail)
+    bool no_trim = false;         // uniform tasks keep their full shape (147 CTAs on 2^24 rows instead of 148 trimmed ones)
 };
 
 constexpr uint32_t kCtaDoneRing = 64;
@@ -602,6 +603,7 @@ int set_tuning(Tuning& t, const char* name, int64_t v) {
         {"host_copy_path", nullptr, &t.host_copy_path, 0, 1},
         {"serial_launch", nullptr, &t.serial_launch, 0, 1},
         {"no_lookahead", nullptr, &t.no_lookahead, 0, 1},
+        {"no_trim", nullptr, &t.no_trim, 0, 1},
     };
     for (auto& e : tab) {
         if (strcmp(e.n, name)) continue;
@@ -923,7 +925,7 @@ void fill_answer_split(pir_db* db, const QueryGeom& g, AnswerPlan* ap, bool thro
     ap->hi_warps = db->split_hiw;
     ap->Dmin = db->split_dmin;
     ap->m_task = 0;
-    if (ap->hi_warps != 0u && !throughput) {
+    if (ap->hi_warps != 0u && !throughput && !db->tune.no_trim) {
         // Trim the tasks so that every SM gets the same number of rows: 2^24 rows in (7, 12) tasks of 114 688 rows are
         // 146.3 tasks, i.e. 147 CTAs of which one is a third full and one SM idle; 148 tasks of 443 (instead of 448)
         // thread-root nodes do 1 % less work each.  Only a light trim: the trailing threads of a task idle.

@@ -18,6 +18,8 @@ while len(found) < 2:
     found.setdefault(q0.final_cw & 1, (q0, q1))
 a = np.zeros(S, np.uint8); b = np.zeros(S, np.uint8); want = np.zeros(S, np.uint8)
 _capi.check(L.pir_db_download(h, 1234567, want.ctypes.data_as(C.c_void_p), 1))
+for name, val in [o.split("=") for o in os.environ.get("OPTS", "").split(",") if o]:   # e.g. OPTS=no_trim=1,no_lookahead=1
+    _capi.check(L.pir_db_set_option(h, name.encode(), int(val)))
 for par, (q0, q1) in sorted(found.items()):
     _capi.check(L.pir_answer(h, C.byref(q0), a.ctypes.data_as(C.c_void_p), S))
     _capi.check(L.pir_answer(h, C.byref(q1), b.ctypes.data_as(C.c_void_p), S))
