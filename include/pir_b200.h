@@ -130,6 +130,19 @@ int pir_answer_batch(pir_db* db, const pir_query* qs, uint32_t n_queries, void* 
 /* ExpandSharedQuery (db.go:110-174): bits_out[r] in {0,1} for the shard's rows, one byte per row
  * like Go's []bool.  n_rows must be the shard's row count for q->group_size. */
 int pir_expand_bits(pir_db* db, const pir_query* q, uint8_t* bits_out, uint64_t n_rows);
+/*
+ * pir_expand_bits without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The same kernels as pir_expand_bits, with their scratch (the packed selection-bit vector) in a file-scope static
+ * device array of PIR_NOALLOC_MAX_ROWS bits (2 MiB, held by every GPU that loads the library until exit) and the result
+ * -- one 0/1 byte per shard row -- written to the CALLER's device buffer d_bits_out (n_rows bytes, 4-byte aligned).
+ * Only enqueues work on `stream` (a cudaStream_t as void*, NULL = the handle's own): no cudaMalloc / cudaFree, no
+ * synchronisation.  Index queries only; n_rows must be the shard's row count and at most PIR_NOALLOC_MAX_ROWS
+ * (PIR_ERR_BAD_ARG beyond it).  ALL calls on one GPU share the array: each call clears what it uses first, and calls
+ * whose GPU work overlaps (different streams, different handles on the same GPU) race -- serialise them.
+ */
+#define PIR_NOALLOC_MAX_ROWS (1ull << 24)
+int pir_expand_bits_noalloc(pir_db* db, const pir_query* q, uint8_t* d_bits_out, uint64_t n_rows, void* stream);
 /* PrivateSecretSharedQueryWithExpandedBits (db.go:75-107). */
 int pir_answer_with_bits(pir_db* db, uint32_t group_size, const uint8_t* bits, uint64_t n_rows,
                          void* out, size_t out_len);

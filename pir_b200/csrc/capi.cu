@@ -112,9 +112,19 @@ const AesHost& aes_host() {
     return a;
 }
 
+// ---- scratch of pir_expand_bits_noalloc --------------------------------------------------------------
+// The packed selection-bit vector that the answer kernel's BITS mode ORs into, as a file-scope device array, so that the
+// entry point needs no cudaMalloc.  2 MiB + 16 bytes in the memory of EVERY GPU that loads this library, until exit.
+// In host code `g_noalloc_bits` is only a stand-in for the symbol, NOT a device address: its device address is taken
+// once per device with cudaGetSymbolAddress (device_ctx below, that device current) and kept in DeviceCtx.
+constexpr uint64_t kNoAllocMaxRows = 1ull << 24;                     // PIR_NOALLOC_MAX_ROWS in include/pir_b200.h
+constexpr uint64_t kNoAllocWords = kNoAllocMaxRows / 32 + 4;         // ceil(rows / 32) + 1 spill word, rounded up to 4
+static __device__ __align__(256) uint32_t g_noalloc_bits[kNoAllocWords];
+
 // ---- per-device context -------------------------------------------------------------------------
 struct DeviceCtx {
     bool ready = false;
+    uint32_t* noalloc_bits = nullptr;  // device address of g_noalloc_bits on this device
     uint32_t* d_t0 = nullptr;
     uint32_t smem_base = 0;
     int num_sms = 0;
@@ -156,6 +166,7 @@ int device_ctx(int device, DeviceCtx** out) {
         CU(configure_kernels());
         CU(probe_smem_base(&c.smem_base));
         if (c.smem_base >= 8192) return fail(PIR_ERR_CUDA, "unexpected dynamic shared memory base %u", c.smem_base);
+        CU(cudaGetSymbolAddress((void**)&c.noalloc_bits, g_noalloc_bits));  // (this device is current: DeviceGuard above)
         c.ready = true;
     }
     *out = &c;
@@ -1271,6 +1282,45 @@ extern "C" int pir_db_time_expansion(pir_db* db, const pir_query* q, uint32_t re
         return fail(PIR_ERR_CUDA, "pir_db_time_expansion: %s", cudaGetErrorString(e));
     }
     *ms_per_launch = (double)ms / (double)reps;
+    return PIR_OK;
+}
+
+// ExpandSharedQuery without any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that forbid it).
+// The same two kernels as pir_expand_bits -- answer_kernel in BITS mode, then unpack_bits_kernel -- with the packed bit
+// vector in the static device array g_noalloc_bits instead of per-handle scratch from cudaMalloc, and the result
+// written to the CALLER's device buffer.  Only enqueues work on `stream`: no cudaMalloc / cudaFree / event or stream
+// creation, no synchronisation.  Every call on a GPU shares the one array: it is cleared at the start of every call
+// (the kernel ORs into it), and two calls that overlap on the GPU race.
+extern "C" int pir_expand_bits_noalloc(pir_db* db, const pir_query* q, uint8_t* d_bits_out, uint64_t n_rows, void* stream) {
+    if (!db || !q || (!d_bits_out && n_rows)) return fail(PIR_ERR_BAD_ARG, "null argument");
+    if (q->is_keyword) return fail(PIR_ERR_UNSUPPORTED, "pir_expand_bits_noalloc takes index queries only (keyword queries use no scratch)");
+    if (((uintptr_t)d_bits_out & 3u) != 0) return fail(PIR_ERR_BAD_ARG, "d_bits_out must be 4-byte aligned");
+    std::lock_guard<std::mutex> lk(db->mu);
+    DeviceGuard g(db->device);
+    QueryGeom geom;
+    int rc = query_geom(db, q, &geom);
+    if (rc) return rc;
+    if (n_rows != geom.n_rows) return fail(PIR_ERR_BAD_ARG, "n_rows %llu != shard rows %llu", (unsigned long long)n_rows,
+                                           (unsigned long long)geom.n_rows);
+    if (n_rows > kNoAllocMaxRows)
+        return fail(PIR_ERR_BAD_ARG, "pir_expand_bits_noalloc: %llu rows exceed the static scratch (PIR_NOALLOC_MAX_ROWS = %llu); "
+                                     "use pir_expand_bits", (unsigned long long)n_rows, (unsigned long long)kNoAllocMaxRows);
+    if (n_rows == 0) return PIR_OK;
+    QueryConst qc;
+    if ((rc = build_query_const(q, geom.nb, &qc))) return rc;
+    const DeviceCtx& ctx = *db->ctx;
+    if (!ctx.noalloc_bits) return fail(PIR_ERR_CUDA, "static scratch was not set up on device %d", db->device);
+    cudaStream_t st = stream ? (cudaStream_t)stream : db->stream;
+    const uint64_t wpq = (((n_rows + 31) >> 5) + 1 + 3) & ~3ull;  // (<= kNoAllocWords by the check above)
+    CU(cudaMemsetAsync(ctx.noalloc_bits, 0, wpq * 4, st));         // the array keeps the last call's bits: start from zero
+    AnswerPlan ap{};
+    ap.db = db->d_slots;
+    ap.row_bytes = 16;  // unused in BITS mode
+    fill_answer_split(db, geom, &ap);
+    ap.bits_out = ctx.noalloc_bits;
+    CU(launch_answer(qc, ap, ctx.d_t0, ctx.smem_base, ctx.num_sms, st));
+    CU(launch_unpack_bits(ctx.noalloc_bits, d_bits_out, n_rows, st));
     return PIR_OK;
 }
 
