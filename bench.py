@@ -14,6 +14,7 @@ ring slot on rank 0's GPU (CUDA IPC mapping over NVLink; no NCCL in the data pat
             other processes through a shared-memory mailbox; every rank launches its shard; rank 0 waits for the N
             arrivals, reads the combined answer and re-zeroes the ring slot (ring of 4) -- all inside the timed loop.
             `e2e_single_process` times pir_server_answer (one process drives all N GPUs: the Go server's path).
+            `e2e_concurrent` (N = 1): pir_answer from 8 host threads at once on one handle (queries in flight overlap).
   roofline  dominant kernel vs measured HBM bandwidth on ALGORITHMIC bytes (rows x row_bytes per launch), plus the
             bound that binds: `lookup` = AES blocks/s against the AES-only rate of the same shard measured in this
             run (BITS-mode launches: same tree expansion, no row read), and `dram` = physical bytes (selected rows
@@ -43,6 +44,8 @@ SEED = 2024
 CPU_SAMPLE_LOG_ROWS = 20
 METRIC = "dpf_pir_answer_db_scan_throughput"
 UNIT = "GB/s"
+CONC = 8            # host threads of the concurrent end-to-end region (N = 1)
+CONC_PASSES = 4     # passes of those threads over the timed keys
 RING = 4            # combine slots of the e2e loop at N > 1 (reset and re-used inside the timed loop)
 
 
@@ -434,6 +437,29 @@ def headline(env, args):
         for i in timed:
             capi.check(L.pir_answer(h, C.byref(key(i)), e2e_ans[i].ctypes.data_as(C.c_void_p), S))
         e2e_ms = (time.perf_counter() - t0) * 1e3
+        # the same host call from CONC threads at once (a loaded server: one goroutine per query in flight).  A call holds
+        # the handle's mutex only while it enqueues; the launches queue up on the GPU, overlap and look ahead.
+        conc_ans = np.zeros((total, S), dtype=np.uint8)
+        conc_err = []
+
+        def conc_worker(t):
+            try:
+                for _ in range(CONC_PASSES):
+                    for i in list(timed)[t::CONC]:
+                        capi.check(L.pir_answer(h, C.byref(key(i)), conc_ans[i].ctypes.data_as(C.c_void_p), S))
+            except Exception as exc:   # noqa: BLE001 (reported below)
+                conc_err.append(exc)
+        for phase in ("warm", "timed"):
+            ths = [threading.Thread(target=conc_worker, args=(t,)) for t in range(CONC)]
+            env.barrier()
+            t0 = time.perf_counter()
+            for th in ths:
+                th.start()
+            for th in ths:
+                th.join()
+            conc_ms = (time.perf_counter() - t0) * 1e3
+        if conc_err:
+            raise SystemExit("bench.py: concurrent pir_answer failed: %s" % conc_err[0])
     else:
         box = Mailbox(env, C.sizeof(capi.PirQuery))
 
@@ -479,6 +505,8 @@ def headline(env, args):
         env.cpu_barrier()
         env.barrier()
 
+    if world > 1:
+        conc_ans, conc_ms = None, None
     dev_ms, e2e_ms, iso_ms, aes_ms = env.max_over_ranks([dev_ms, e2e_ms, iso_ms, aes_ms])
 
     # ---- parity: every timed answer against the oracle's bytes (outside the timed regions) ----
@@ -486,7 +514,7 @@ def headline(env, args):
     if rank == 0:
         want, mean_sel = oracle_answers(env, n, S, SEED, [key(i) for i in timed])
         for k, i in enumerate(timed):
-            for name, got in (("device-timed", dev_ans), ("e2e", e2e_ans), ("single-process", sp_ans)):
+            for name, got in (("device-timed", dev_ans), ("e2e", e2e_ans), ("single-process", sp_ans), ("concurrent e2e", conc_ans)):
                 if got is not None and not np.array_equal(got[i], want[k]):
                     raise SystemExit("bench.py: %s answer of step %d (server %d) differs from the oracle's bytes -- "
                                      "refusing to report a wrong path" % (name, i, i & 1))
@@ -555,6 +583,12 @@ def headline(env, args):
                                   "frac": phys / (ms_step * 1e-3) / 1e9 / peak}},
             "clocks": clocks,
         }
+        if conc_ms is not None:
+            per = conc_ms / (args.steps * CONC_PASSES)
+            line["e2e_concurrent"] = {"value": db_bytes / (per * 1e-3) / 1e9, "unit": UNIT, "ms_per_query": per, "queries_per_s": 1e3 / per,
+                                      "threads": CONC, "queries": args.steps * CONC_PASSES,
+                                      "api": "pir_answer (host key in / host answer out) from %d host threads at once on ONE handle: each call "
+                                             "enqueues under the handle's mutex and waits for its own event with the mutex released" % CONC}
         if sp_ms is not None:
             line["e2e_single_process"] = {"value": db_bytes / (sp_ms / args.steps * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": sp_ms / args.steps,
                                           "api": "pir_server_answer: ONE process (rank 0) drives all %d GPUs, host key in / host answer out; the other "

@@ -173,6 +173,11 @@ __device__ __forceinline__ void scan_group(const AnswerPlan& ap, const ScanLane&
     // byte address of the group's first row, for this lane's 16-byte chunk (rows before the shard's
     // first row are never selected, so a negative offset is never dereferenced)
     const uint8_t* gbase = sl.lane_db + group_row0 * (int64_t)ap.row_bytes;
+#ifdef PIRB_TEX_ROWS
+    // texel (16-byte chunk) index of this lane's chunk of the group's first row; rows of the shard lie below 2^28 texels
+    const int tbase = (int)((int64_t)sl.chunk + group_row0 * (int64_t)(ap.row_bytes >> 4));
+    const int trow = (int)(ap.row_bytes >> 4);
+#endif
     // The list is kept as rpl interleaved sub-lists (entry p goes to sub-list p % rpl, the lane group that
     // will fetch it), so a lane group reads its next 8 row numbers with ONE 128-bit shared load.
     uint32_t pos = pre - cnt;
@@ -208,7 +213,11 @@ __device__ __forceinline__ void scan_group(const AnswerPlan& ap, const ScanLane&
                     const uint32_t e = eb + (uint32_t)u * sl.rpl + sl.h;
                     const uint32_t row = (lw[u >> 1] >> ((u & 1) * 16)) & 0xffffu;
                     v[k * 8 + u] = make_uint4(0, 0, 0, 0);
+#ifdef PIRB_TEX_ROWS
+                    if (e < my_total) v[k * 8 + u] = tex1Dfetch<uint4>((cudaTextureObject_t)ap.tex, tbase + cb * 32 + (int)row * trow);
+#else
                     if (e < my_total) v[k * 8 + u] = ldg_nc_v4(cbase + (uint64_t)row * ap.row_bytes);
+#endif
                 }
             }
 #pragma unroll

@@ -8,6 +8,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <atomic>
+#include <condition_variable>
 #include <initializer_list>
 #include <mutex>
 #include <new>
@@ -243,6 +244,7 @@ struct Tuning {
 };
 
 constexpr uint32_t kCtaDoneRing = 64;
+constexpr uint32_t kHostRing = 8;  // single-query host calls in flight per handle
 constexpr size_t kAnswerMaxRowBytes = 4096;  // widest row the warp-specialised kernel takes (answer_kernel_supports)
 
 struct pir_db {
@@ -286,6 +288,17 @@ struct pir_db {
     LaTop* d_tops = nullptr;
     LaMail* d_mail = nullptr;
     uint64_t la_seq = 0;
+    // Host calls in flight (pir_answer from several threads): a ring of pinned, device-mapped answer slots, one event
+    // each.  A caller enqueues its launch under the handle's mutex, then waits for ITS event with the mutex released,
+    // so the launches of concurrent callers queue up behind each other on the GPU (and overlap / look ahead, 4.1).
+    uint8_t* h_ring = nullptr;
+    uint8_t* h_ring_dev = nullptr;
+    cudaEvent_t ring_ev[kHostRing] = {};
+    uint32_t ring_busy = 0;  // bit k: slot k belongs to a caller
+    std::condition_variable ring_cv;
+#ifdef PIRB_TEX_ROWS
+    cudaTextureObject_t tex = 0;  // experiment: linear uint4 texture over d_slots (0 if the shard exceeds the texel limit)
+#endif
     uint64_t h_out_cap = 0;
     // cached work split of the answer kernel for the last (num_bits, shard rows) seen
     uint32_t split_nb = 0, split_d = 0, split_hiw = 0, split_dmin = 0;
@@ -518,6 +531,13 @@ extern "C" int pir_db_create(int device, uint64_t db_size, uint32_t slot_bytes, 
     if (e == cudaSuccess) e = cudaMalloc(&db->d_cta_done, kCtaDoneRing * sizeof(uint32_t));
     if (e == cudaSuccess) e = cudaMemsetAsync(db->d_cta_done, 0, kCtaDoneRing * sizeof(uint32_t), db->stream);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&db->acc_ev, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaHostAlloc(&db->h_ring, kHostRing * kAnswerMaxRowBytes, cudaHostAllocMapped);
+    if (e == cudaSuccess) {
+        void* dp = nullptr;
+        if (cudaHostGetDevicePointer(&dp, db->h_ring, 0) == cudaSuccess) db->h_ring_dev = (uint8_t*)dp;
+        else cudaGetLastError();  // (no mapped access: host calls keep the memset + kernel + copy path)
+    }
+    for (uint32_t k = 0; k < kHostRing && e == cudaSuccess; k++) e = cudaEventCreateWithFlags(&db->ring_ev[k], cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaHostAlloc(&db->h_mail, kLaMailRing * sizeof(LaMail), cudaHostAllocMapped);
     if (e == cudaSuccess) {
         memset(db->h_mail, 0, kLaMailRing * sizeof(LaMail));
@@ -528,6 +548,26 @@ extern "C" int pir_db_create(int device, uint64_t db_size, uint32_t slot_bytes, 
     const size_t tops_bytes = (size_t)kLaTopRing * (size_t)ctx->num_sms * sizeof(LaTop);
     if (e == cudaSuccess) e = cudaMalloc(&db->d_tops, tops_bytes);
     if (e == cudaSuccess) e = cudaMemsetAsync(db->d_tops, 0, tops_bytes, db->stream);
+#ifdef PIRB_TEX_ROWS
+    if (e == cudaSuccess && bytes) {
+        cudaChannelFormatDesc cd = cudaCreateChannelDesc(32, 32, 32, 32, cudaChannelFormatKindUnsigned);
+        size_t max_texels = 0;
+        if (cudaDeviceGetTexture1DLinearMaxWidth(&max_texels, &cd, device) != cudaSuccess) max_texels = 0, cudaGetLastError();
+        if (bytes / 16 <= max_texels) {
+            cudaResourceDesc rd{};
+            rd.resType = cudaResourceTypeLinear;
+            rd.res.linear.devPtr = db->d_slots;
+            rd.res.linear.desc = cd;
+            rd.res.linear.sizeInBytes = bytes;
+            cudaTextureDesc td{};
+            td.readMode = cudaReadModeElementType;
+            td.filterMode = cudaFilterModePoint;
+            td.addressMode[0] = cudaAddressModeClamp;
+            e = cudaCreateTextureObject(&db->tex, &rd, &td, nullptr);
+        }
+        fprintf(stderr, "[tex] shard of %llu texels, limit %zu, texture %s\n", (unsigned long long)(bytes / 16), max_texels, db->tex ? "on" : "off");
+    }
+#endif
     if (e == cudaSuccess) e = cudaMalloc(&db->d_mail, kLaTopRing * sizeof(LaMail));
     if (e == cudaSuccess) e = cudaMemsetAsync(db->d_mail, 0, kLaTopRing * sizeof(LaMail), db->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(db->stream);
@@ -555,8 +595,14 @@ extern "C" int pir_db_destroy(pir_db* db) {
     if (db->d_cta_done) cudaFree(db->d_cta_done);
     if (db->d_acc) cudaFree(db->d_acc);
     if (db->acc_ev) cudaEventDestroy(db->acc_ev);
+    if (db->h_ring) cudaFreeHost(db->h_ring);
+    for (uint32_t k = 0; k < kHostRing; k++)
+        if (db->ring_ev[k]) cudaEventDestroy(db->ring_ev[k]);
     if (db->d_tops) cudaFree(db->d_tops);
     if (db->d_mail) cudaFree(db->d_mail);
+#ifdef PIRB_TEX_ROWS
+    if (db->tex) cudaDestroyTextureObject(db->tex);
+#endif
     if (db->h_mail) cudaFreeHost(db->h_mail);
     for (int k = 0; k < 2; k++)
         if (db->side[k]) cudaStreamDestroy(db->side[k]);
@@ -797,6 +843,10 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
         ap.db = db->d_slots;
         ap.row_bytes = g.row_bytes;
         fill_answer_split(db, g, &ap, throughput);
+#ifdef PIRB_TEX_ROWS
+        ap.tex = db->tex;
+        if (!db->tex) return fail(PIR_ERR_UNSUPPORTED, "PIRB_TEX_ROWS build: shard too large for a linear texture");
+#endif
         ap.out = (uint32_t*)d_out;
         if (final_out) {  // (the caller has checked that this branch will be taken: single_launch_ok; d_out is db->d_acc)
             if (db->acc_stream && db->acc_stream != st) {
@@ -1118,28 +1168,40 @@ extern "C" int pir_answer_batch_device(pir_db* db, const pir_query* qs, uint32_t
 
 extern "C" int pir_answer_batch(pir_db* db, const pir_query* qs, uint32_t n_queries, void* out, size_t out_len) {
     if (!db || !qs || !out || n_queries == 0) return fail(PIR_ERR_BAD_ARG, "null or empty argument");
-    std::lock_guard<std::mutex> lk(db->mu);
+    std::unique_lock<std::mutex> lk(db->mu);
     DeviceGuard g(db->device);
     QueryGeom g0;
     int rc = query_geom(db, &qs[0], &g0);
     if (rc) return rc;
     const size_t ans = (size_t)g0.W * db->slot_bytes;
     if (out_len < ans * n_queries) return fail(PIR_ERR_BAD_ARG, "out_len %zu < %zu", out_len, ans * n_queries);
+    // One index query answered by the warp-specialised kernel: its last CTA writes the answer straight into a pinned host
+    // slot and re-zeroes the device accumulator, so the call is one launch and one wait -- for the caller's OWN event,
+    // with the handle's mutex released: calls from several threads are in flight together (kHostRing at most).
+    if (n_queries == 1 && db->h_ring_dev && single_launch_ok(db, &qs[0], g0)) {
+        db->ring_cv.wait(lk, [&] { return db->ring_busy != (1u << kHostRing) - 1u; });
+        uint32_t k = 0;
+        while ((db->ring_busy >> k) & 1u) k++;
+        db->ring_busy |= 1u << k;
+        uint8_t* slot = db->h_ring + (size_t)k * kAnswerMaxRowBytes;
+        rc = enqueue_answer(db, &qs[0], g0, db->d_acc, db->stream, /*zero_first=*/false, nullptr, nullptr, false,
+                            (uint32_t*)(db->h_ring_dev + (size_t)k * kAnswerMaxRowBytes));
+        cudaError_t e = cudaEventRecord(db->ring_ev[k], db->stream);
+        lk.unlock();
+        if (e == cudaSuccess) e = cudaEventSynchronize(db->ring_ev[k]);
+        if (e != cudaSuccess && rc == PIR_OK) rc = fail(PIR_ERR_CUDA, "answer kernel failed: %s", cudaGetErrorString(e));
+        if (rc == PIR_OK) compact_answer(db, g0.W, slot, (uint8_t*)out);
+        lk.lock();
+        db->ring_busy &= ~(1u << k);
+        db->ring_cv.notify_one();
+        return rc;
+    }
     if ((rc = ensure_out(db, g0.row_bytes * n_queries))) return rc;
     for (uint32_t i = 0; i < n_queries; i++) {
         QueryGeom geom;
         if ((rc = query_geom(db, &qs[i], &geom))) return rc;
         if (qs[i].group_size != qs[0].group_size || qs[i].is_keyword != qs[0].is_keyword)
             return fail(PIR_ERR_BAD_ARG, "all queries of a batch must share group_size and is_keyword");
-    }
-    // One index query answered by the warp-specialised kernel: its last CTA writes the answer straight into the pinned
-    // host buffer and re-zeroes the device accumulator, so the call is one launch and one stream synchronisation.
-    if (n_queries == 1 && db->h_out_dev && single_launch_ok(db, &qs[0], g0)) {
-        rc = enqueue_answer(db, &qs[0], g0, db->d_acc, db->stream, /*zero_first=*/false, nullptr, nullptr, false, db->h_out_dev);
-        if (cudaStreamSynchronize(db->stream) != cudaSuccess && rc == PIR_OK) rc = fail(PIR_ERR_CUDA, "answer kernel failed: %s", cudaGetErrorString(cudaGetLastError()));
-        if (rc) return rc;
-        compact_answer(db, g0.W, db->h_out, (uint8_t*)out);
-        return PIR_OK;
     }
     if (batch_uses_bits_path(db, qs, n_queries, g0)) {
         if ((rc = enqueue_batch_bits(db, qs, n_queries, g0, db->d_out, db->stream))) {

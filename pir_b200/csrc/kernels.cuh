@@ -98,6 +98,10 @@ struct AnswerPlan {
     const LaMail* la_mail;
     LaMail* la_dmail;     // [kLaTopRing] in device memory: CTA 0 republishes the next launch's mail here for the other CTAs
     LaTop* la_tops;
+#ifdef PIRB_TEX_ROWS
+    // experiment: rows fetched through the texture path; a linear texture of uint4 texels over `db`
+    unsigned long long tex;
+#endif
 };
 
 // The in-kernel phase counters (clock64 / globaltimer) and the experiment flags exist in the PIRB_DEV build only

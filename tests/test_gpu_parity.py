@@ -448,3 +448,47 @@ def test_any_row_size_takes_the_warp_specialised_kernel(gpu_lib, slot_bytes, W):
             assert np.array_equal(both[3], w1) and np.array_equal(both[4], w0)
             h.set_option("kernel_v1", 1)
             assert np.array_equal(h.answer(q0), w0)
+
+
+def test_concurrent_host_calls_on_one_handle(gpu_lib):
+    """pir_answer from 12 threads at once on ONE handle (more threads than the handle's ring of 8 in-flight host
+    slots): every call enqueues under the handle's mutex and waits for its own event with the mutex released, so the
+    launches overlap on the GPU.  Every answer must equal the oracle's; mixed with batch and expand calls of other
+    threads that take the other paths."""
+    import threading
+    n, S = 1 << 17, 256
+    data = oracle.synth_fill(55, 0, n, S)
+    rng = np.random.default_rng(17)
+    pairs = [make_queries(4000 + k, n, 1, int(rng.integers(0, n))) for k in range(24)]
+    keys = [(p[0][s], p[1][s]) for p in pairs for s in (0, 1)]
+    want = [oracle.answer(o, data, n, S, use_tree=True) for o, _ in keys]
+    errors = []
+    with Handle(n, S) as h:
+        h.fill(55)
+
+        def single(t):
+            try:
+                for rep in range(3):
+                    for k in range(t, len(keys), 12):
+                        if not np.array_equal(h.answer(keys[k][1]), want[k]):
+                            errors.append(("single", t, rep, k))
+            except Exception as exc:   # noqa: BLE001
+                errors.append(("single", t, repr(exc)))
+
+        def other(t):
+            try:
+                for rep in range(3):
+                    got = h.answer_batch([keys[t][1], keys[t + 1][1], keys[t + 2][1]])
+                    if not (np.array_equal(got[0], want[t]) and np.array_equal(got[2], want[t + 2])):
+                        errors.append(("batch", t, rep))
+                    if not np.array_equal(h.expand_bits(keys[t][1]), oracle.expand_tree(keys[t][0], n)):
+                        errors.append(("bits", t, rep))
+            except Exception as exc:   # noqa: BLE001
+                errors.append(("other", t, repr(exc)))
+        ths = [threading.Thread(target=single, args=(t,)) for t in range(12)] + [threading.Thread(target=other, args=(t,)) for t in (0, 5)]
+        for th in ths:
+            th.start()
+        for th in ths:
+            th.join(timeout=120)
+        assert not any(th.is_alive() for th in ths), "a thread hung"
+    assert not errors, errors[:5]

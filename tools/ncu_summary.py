@@ -11,6 +11,8 @@ KEEP = re.compile(
     r"^(gpu__time_duration\.sum|dram__bytes_(read|write)\.sum|launch__(registers_per_thread|grid_size|block_size|"
     r"shared_mem_per_block_dynamic)|sm__cycles_(active|elapsed)\.avg|"
     r"l1tex__data_pipe_lsu_wavefronts(_mem_shared(_op_(ld|st))?|_mem_lgds)?\.(sum|avg)(\.pct_of_peak_sustained_elapsed)?|"
+    r"l1tex__data_pipe_tex_wavefronts(_mem_\w+)?\.(sum|avg)(\.pct_of_peak_sustained_elapsed)?|l1tex__tex_writeback_active\.avg\.pct_of_peak_sustained_elapsed|"
+    r"l1tex__texin_\w+\.(sum|avg)(\.pct_of_peak_sustained_elapsed)?|smsp__inst_executed_pipe_tex\.sum|sm__inst_executed_pipe_tex\.avg\.pct_of_peak_sustained_active|"
     r"l1tex__lsu_writeback_active\.avg\.pct_of_peak_sustained_elapsed|l1tex__data_bank_(reads|writes)\.avg\.pct_of_peak_sustained_elapsed|"
     r"l1tex__data_bank_conflicts_pipe_lsu_mem_shared(_op_(ld|st))?\.sum|"
     r"sm__inst_executed_pipe_(alu|fma|lsu|xu|adu|uniform)\.avg\.pct_of_peak_sustained_active|"

@@ -3,6 +3,8 @@ import ctypes as C, os, sys
 import numpy as np
 sys.path.insert(0, os.getcwd())
 from pir_b200 import _capi
+if os.environ.get("VARIANT_SO"):     # A/B of library builds; a tool-side switch, not the product's
+    _capi.LIB_PATH = os.environ["VARIANT_SO"]
 L = _capi.lib()
 n, S = 1 << 24, 256
 nb = L.pir_num_bits_for(n, 1, 0)
