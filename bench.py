@@ -13,6 +13,7 @@ ring slot on rank 0's GPU (CUDA IPC mapping over NVLink; no NCCL in the data pat
             memory.  N = 1: pir_answer.  N > 1: the key lives in rank 0's host memory only and is fanned out to the
             other processes through a shared-memory mailbox; every rank launches its shard; rank 0 waits for the N
             arrivals, reads the combined answer and re-zeroes the ring slot (ring of 4) -- all inside the timed loop.
+            `e2e_pipelined` (N > 1): the same loop with 4 queries in flight.
             `e2e_single_process` times pir_server_answer (one process drives all N GPUs: the Go server's path).
             `e2e_concurrent` (N = 1): pir_answer from 8 host threads at once on one handle (queries in flight overlap).
   roofline  dominant kernel vs measured HBM bandwidth on ALGORITHMIC bytes (rows x row_bytes per launch), plus the
@@ -46,6 +47,8 @@ METRIC = "dpf_pir_answer_db_scan_throughput"
 UNIT = "GB/s"
 CONC = 8            # host threads of the concurrent end-to-end region (N = 1)
 CONC_PASSES = 4     # passes of those threads over the timed keys
+PIPE_DEPTH = 4      # queries in flight in the pipelined end-to-end region (N > 1)
+PIPE_RING = 8       # its combine slots (a slot is re-used 8 queries later, after its answer has been read and it was re-zeroed)
 RING = 4            # combine slots of the e2e loop at N > 1 (reset and re-used inside the timed loop)
 
 
@@ -315,14 +318,17 @@ def oracle_answers(env, n, S, seed, queries):
 
 class Mailbox:
     """Query fan-out for the one-process-per-GPU layout: the key arrives in rank 0's host memory only; rank 0 writes it
-    (1256 bytes + a sequence number) into a POSIX shared-memory segment, the other ranks poll the sequence number."""
+    (1256 bytes) into slot seq % SLOTS of a POSIX shared-memory ring and then bumps a sequence number; the other ranks
+    poll the sequence number.  A slot is re-used SLOTS queries later, which the caller's flow control makes safe."""
+    SLOTS = 8
 
     def __init__(self, env, qbytes):
         from multiprocessing import shared_memory
         np = env.np
         name = "pirb_bench_%s" % os.environ.get("MASTER_PORT", "0")
         self.env, self.qbytes = env, qbytes
-        self.off = (qbytes + 63) // 64 * 64      # the sequence number sits in its own cache line behind the key
+        self.pitch = (qbytes + 63) // 64 * 64
+        size = self.SLOTS * self.pitch + 64        # the sequence number sits in its own cache line behind the keys
         if env.rank == 0:
             try:
                 old = shared_memory.SharedMemory(name=name)
@@ -330,17 +336,17 @@ class Mailbox:
                 old.unlink()
             except FileNotFoundError:
                 pass
-            self.shm = shared_memory.SharedMemory(name=name, create=True, size=self.off + 64)
-            self.shm.buf[:self.off + 64] = bytes(self.off + 64)
+            self.shm = shared_memory.SharedMemory(name=name, create=True, size=size)
+            self.shm.buf[:size] = bytes(size)
         env.barrier()
         if env.rank != 0:
             self.shm = shared_memory.SharedMemory(name=name)
-        self.payload = np.ndarray((qbytes,), dtype=np.uint8, buffer=self.shm.buf, offset=0)
-        self.seq = np.ndarray((1,), dtype=np.uint64, buffer=self.shm.buf, offset=self.off)
+        self.payload = np.ndarray((self.SLOTS, self.pitch), dtype=np.uint8, buffer=self.shm.buf, offset=0)
+        self.seq = np.ndarray((1,), dtype=np.uint64, buffer=self.shm.buf, offset=self.SLOTS * self.pitch)
         env.barrier()
 
     def publish(self, q, seq):
-        self.payload[:] = self.env.np.frombuffer(q.to_bytes(), dtype=self.env.np.uint8)
+        self.payload[seq % self.SLOTS, :self.qbytes] = self.env.np.frombuffer(q.to_bytes(), dtype=self.env.np.uint8)
         self.seq[0] = seq
 
     def receive(self, seq, timeout_s=30.0):
@@ -348,7 +354,7 @@ class Mailbox:
         while int(self.seq[0]) < seq:
             if time.perf_counter() - t0 > timeout_s:
                 raise SystemExit("bench.py: rank %d timed out waiting for query %d" % (self.env.rank, seq))
-        return self.env.capi.PirQuery.from_bytes(self.payload.tobytes())
+        return self.env.capi.PirQuery.from_bytes(self.payload[seq % self.SLOTS, :self.qbytes].tobytes())
 
     def close(self):
         del self.payload, self.seq
@@ -377,7 +383,7 @@ def headline(env, args):
     if world > 1:
         # ring slots on rank 0's GPU: [0, total) one per device-timed step, [total, total + RING) re-used by the e2e loop,
         # one scratch slot; every rank's kernel XORs its partial straight into them (CUDA IPC mapping, NVLink)
-        comb = env.sharding.open_combine_over_group(env.dist, env.local, total + RING + 1, S, owner=0)
+        comb = env.sharding.open_combine_over_group(env.dist, env.local, total + RING + 1 + PIPE_RING, S, owner=0)
 
     def step_device(i, slot=None):
         if world > 1:
@@ -484,11 +490,42 @@ def headline(env, args):
         env.torch.cuda.synchronize()
         e2e_ms = (time.perf_counter() - t0) * 1e3
         env.barrier()
+        # ---- the same end to end with PIPE_DEPTH queries in flight: rank 0 publishes query seq, every rank launches it,
+        #      and rank 0 collects the answer of query seq - (PIPE_DEPTH - 1) (wait for its N arrivals, host copy, slot
+        #      re-zeroed).  A combine slot / mailbox slot is re-used PIPE_RING queries later, after its answer was read.
+        pipe_ans = np.zeros((total, S), dtype=np.uint8)
+        pslot = lambda sq: total + RING + 1 + (sq % PIPE_RING)
+
+        def pipelined(idx_list, seq):
+            pending = []
+            for i in idx_list:
+                seq += 1
+                if rank == 0:
+                    box.publish(key(i), seq)
+                    q = key(i)
+                else:
+                    q = box.receive(seq)
+                comb.accumulate(h, q, pslot(seq), None)
+                if rank == 0:
+                    pending.append((i, seq))
+                    if len(pending) >= PIPE_DEPTH:
+                        i0, s0 = pending.pop(0)
+                        pipe_ans[i0] = comb.wait_read_reset(pslot(s0), world, S)
+            for i0, s0 in pending:
+                pipe_ans[i0] = comb.wait_read_reset(pslot(s0), world, S)
+            env.torch.cuda.synchronize()
+            return seq
+        seq = pipelined(list(range(min(3, args.warmup))), seq)
+        env.barrier()
+        t0 = time.perf_counter()
+        seq = pipelined(list(timed), seq)
+        pipe_ms = (time.perf_counter() - t0) * 1e3
+        env.barrier()
         box.close()
     clocks = sampler.stop() if rank == 0 else None
 
     # ---- N > 1: the single-process path (one process drives all N GPUs: what a Go server calls) ----
-    sp_ms, sp_ans = None, None
+    sp_ms, sp_ans, spc_ms, spc_ans = None, None, None, None
     if world > 1:
         env.barrier()
         env.cpu_barrier()       # every rank's GPU is idle from here on; the others wait on the host (gloo), not in an NCCL kernel
@@ -502,11 +539,35 @@ def headline(env, args):
                 for i in timed:
                     sp_ans[i] = srv.answer(key(i))
                 sp_ms = (time.perf_counter() - t0) * 1e3
+                # the same call from CONC host threads at once (a Go server with one goroutine per query in flight)
+                spc_ans = np.zeros((total, S), dtype=np.uint8)
+                spc_err = []
+
+                def spc_worker(t):
+                    try:
+                        for _ in range(CONC_PASSES):
+                            for i in list(timed)[t::CONC]:
+                                spc_ans[i] = srv.answer(key(i))
+                    except Exception as exc:   # noqa: BLE001 (reported below)
+                        spc_err.append(exc)
+                for phase in ("warm", "timed"):
+                    ths = [threading.Thread(target=spc_worker, args=(t,)) for t in range(CONC)]
+                    t0 = time.perf_counter()
+                    for th in ths:
+                        th.start()
+                    for th in ths:
+                        th.join()
+                    spc_ms = (time.perf_counter() - t0) * 1e3
+                if spc_err:
+                    raise SystemExit("bench.py: concurrent pir_server_answer failed: %s" % spc_err[0])
         env.cpu_barrier()
         env.barrier()
 
     if world > 1:
         conc_ans, conc_ms = None, None
+        pipe_ms = env.max_over_ranks([pipe_ms])[0]
+    else:
+        pipe_ans, pipe_ms = None, None
     dev_ms, e2e_ms, iso_ms, aes_ms = env.max_over_ranks([dev_ms, e2e_ms, iso_ms, aes_ms])
 
     # ---- parity: every timed answer against the oracle's bytes (outside the timed regions) ----
@@ -514,7 +575,8 @@ def headline(env, args):
     if rank == 0:
         want, mean_sel = oracle_answers(env, n, S, SEED, [key(i) for i in timed])
         for k, i in enumerate(timed):
-            for name, got in (("device-timed", dev_ans), ("e2e", e2e_ans), ("single-process", sp_ans), ("concurrent e2e", conc_ans)):
+            for name, got in (("device-timed", dev_ans), ("e2e", e2e_ans), ("single-process", sp_ans), ("concurrent e2e", conc_ans),
+                              ("pipelined e2e", pipe_ans), ("concurrent single-process", spc_ans)):
                 if got is not None and not np.array_equal(got[i], want[k]):
                     raise SystemExit("bench.py: %s answer of step %d (server %d) differs from the oracle's bytes -- "
                                      "refusing to report a wrong path" % (name, i, i & 1))
@@ -589,10 +651,22 @@ def headline(env, args):
                                       "threads": CONC, "queries": args.steps * CONC_PASSES,
                                       "api": "pir_answer (host key in / host answer out) from %d host threads at once on ONE handle: each call "
                                              "enqueues under the handle's mutex and waits for its own event with the mutex released" % CONC}
+        if pipe_ms is not None:
+            per = pipe_ms / args.steps
+            line["e2e_pipelined"] = {"value": db_bytes / (per * 1e-3) / 1e9, "unit": UNIT, "ms_per_query": per, "queries_per_s": 1e3 / per,
+                                     "in_flight": PIPE_DEPTH,
+                                     "api": "as e2e (key fanned out from rank 0's host memory, pir_answer_accumulate_device on every rank, "
+                                            "pir_combine_wait_read_reset on rank 0), with %d queries in flight: rank 0 collects answer k - %d "
+                                            "after launching query k; combine ring of %d slots re-used inside the loop" % (
+                                                PIPE_DEPTH, PIPE_DEPTH - 1, PIPE_RING)}
         if sp_ms is not None:
             line["e2e_single_process"] = {"value": db_bytes / (sp_ms / args.steps * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": sp_ms / args.steps,
                                           "api": "pir_server_answer: ONE process (rank 0) drives all %d GPUs, host key in / host answer out; the other "
                                                  "ranks idle meanwhile" % world}
+            per = spc_ms / (args.steps * CONC_PASSES)
+            line["e2e_single_process_concurrent"] = {"value": db_bytes / (per * 1e-3) / 1e9, "unit": UNIT, "ms_per_query": per,
+                                                     "queries_per_s": 1e3 / per, "threads": CONC,
+                                                     "api": "pir_server_answer from %d host threads at once on ONE server handle" % CONC}
     # ---- batches: >= 32 queries in flight (queries/s) ----
     NQ = 32
     qb = (capi.PirQuery * NQ)(*[qs[2 * (k % total) + (k & 1)] for k in range(NQ)])

@@ -1265,9 +1265,16 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
     if constexpr (NCB != 0) {  // (BITS mode has nothing to fold)
         __syncthreads();
         asm volatile("griddepcontrol.wait;" ::: "memory");
-        for (uint32_t i = threadIdx.x; i < words_out; i += kAnswerThreads) {
-            const uint32_t v = red[i];
-            if (v) atomicXor(&ap.out[i], v);
+        if (ap.arrivals) {  // (the slot may live on a peer GPU and several GPUs XOR into it: system scope)
+            for (uint32_t i = threadIdx.x; i < words_out; i += kAnswerThreads) {
+                const uint32_t v = red[i];
+                if (v) asm volatile("red.relaxed.sys.global.xor.b32 [%0], %1;" ::"l"(ap.out + i), "r"(v) : "memory");
+            }
+        } else {
+            for (uint32_t i = threadIdx.x; i < words_out; i += kAnswerThreads) {
+                const uint32_t v = red[i];
+                if (v) atomicXor(&ap.out[i], v);
+            }
         }
         if (ap.final_out) {
             // Single-GPU call: every CTA's XORs are fenced and counted; the last CTA reads the finished words
@@ -1289,17 +1296,24 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
                 __threadfence_system();
             }
         } else if (ap.arrivals) {
-            // Multi-GPU combine: this shard's partial is complete once every CTA's XORs are visible.  Each thread
-            // fences its own atomics (the slot may live on a peer GPU), the CTA counts itself in, and the last
-            // CTA of the launch publishes the arrival (kernels.cu wait_arrivals_kernel acquires it on the owner).
+            // Multi-GPU combine: this shard's partial is complete once every CTA's XORs are visible.  The CTA's
+            // threads meet at a barrier and ONE thread fences with system scope (the fence is cumulative over what
+            // the barrier ordered before it: the pattern of a cooperative-groups grid sync and of NCCL's flag stores;
+            // round 1 had all 640 threads execute the system fence), counts the CTA in with release/acquire at GPU
+            // scope, and the last CTA of the launch publishes the arrival with a system-scope release
+            // (kernels.cu wait kernels acquire it on the owner).
             // (Folding the CTAs' partials in local memory first and forwarding one sum per shard was measured on
             // 8 GPUs: no difference, the 148 x 64 remote atomics per shard are not a bottleneck.)
-            __threadfence_system();
             __syncthreads();
-            if (threadIdx.x == 0 && atomicAdd(ap.cta_done, 1u) == gridDim.x - 1u) {
-                *ap.cta_done = 0u;  // ready for the launch that reuses this counter
-                __threadfence_system();
-                atomicAdd_system(ap.arrivals, 1u);
+            if (threadIdx.x == 0) {
+                uint32_t old;
+                asm volatile("fence.acq_rel.sys;" ::: "memory");
+                asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(old) : "l"(ap.cta_done) : "memory");
+                if (old == gridDim.x - 1u) {
+                    *ap.cta_done = 0u;  // ready for the launch that reuses this counter
+                    asm volatile("fence.acq_rel.sys;" ::: "memory");
+                    asm volatile("red.release.sys.global.add.u32 [%0], 1;" ::"l"(ap.arrivals) : "memory");
+                }
             }
         }
     }

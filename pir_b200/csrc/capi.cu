@@ -1859,6 +1859,19 @@ struct pir_server {
     uint8_t* h_acc = nullptr;        // pinned
     cudaStream_t stream = nullptr;   // owner stream
     std::mutex mu;
+    // Single index queries (pir_server_answer): a ring of kHostRing combine slots on the owner device, each with an arrival
+    // counter, a pinned host slot and an event.  Every shard's kernel XORs into slot k and its last CTA bumps the counter
+    // (one launch per shard, no memset, no per-shard event); ONE kernel on the owner waits for the arrivals, moves the
+    // answer to the pinned slot and leaves slot and counter zeroed.  A caller enqueues under the server's mutex and waits
+    // for its own event with the mutex released, so queries of several threads are in flight together.
+    uint8_t* d_ring = nullptr;       // [kHostRing][kAnswerMaxRowBytes] + [kHostRing] u32 arrivals, zero between queries
+    uint8_t* h_ring = nullptr;       // pinned, mapped: [kHostRing][kAnswerMaxRowBytes + 16] (answer + time-out flag)
+    uint8_t* h_ring_dev = nullptr;
+    cudaEvent_t ring_ev[kHostRing] = {};
+    uint32_t ring_busy = 0;
+    std::condition_variable ring_cv;
+    int clock_khz = 0;
+    uint32_t* ring_arrivals(uint32_t k) const { return (uint32_t*)(d_ring + (size_t)kHostRing * kAnswerMaxRowBytes) + k; }
 };
 
 namespace {
@@ -1923,6 +1936,19 @@ extern "C" int pir_server_create(const int* devices, int n_devices, uint64_t db_
         DeviceGuard g(s->owner_device);
         cudaError_t e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&s->zeroed, cudaEventDisableTiming);
+        const size_t ring_bytes = (size_t)kHostRing * kAnswerMaxRowBytes + kHostRing * 4;
+        if (e == cudaSuccess) e = cudaMalloc(&s->d_ring, ring_bytes);
+        if (e == cudaSuccess) e = cudaMemsetAsync(s->d_ring, 0, ring_bytes, s->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
+        if (e == cudaSuccess) e = cudaHostAlloc(&s->h_ring, kHostRing * (kAnswerMaxRowBytes + 16), cudaHostAllocMapped);
+        if (e == cudaSuccess) {
+            memset(s->h_ring, 0, kHostRing * (kAnswerMaxRowBytes + 16));
+            void* dp = nullptr;
+            if (cudaHostGetDevicePointer(&dp, s->h_ring, 0) == cudaSuccess) s->h_ring_dev = (uint8_t*)dp;
+            else cudaGetLastError();
+        }
+        for (uint32_t k = 0; k < kHostRing && e == cudaSuccess; k++) e = cudaEventCreateWithFlags(&s->ring_ev[k], cudaEventDisableTiming);
+        if (e == cudaSuccess && !s->shards.empty()) s->clock_khz = s->shards[0]->ctx->clock_khz;
         if (e != cudaSuccess) rc = fail(PIR_ERR_CUDA, "pir_server_create: %s", cudaGetErrorString(e));
     }
     for (size_t i = 0; i < s->shards.size() && rc == PIR_OK; i++) {
@@ -1957,6 +1983,10 @@ extern "C" int pir_server_destroy(pir_server* s) {
             cudaStreamDestroy(s->stream);
         }
         if (s->zeroed) cudaEventDestroy(s->zeroed);
+        if (s->d_ring) cudaFree(s->d_ring);
+        if (s->h_ring) cudaFreeHost(s->h_ring);
+        for (uint32_t k = 0; k < kHostRing; k++)
+            if (s->ring_ev[k]) cudaEventDestroy(s->ring_ev[k]);
         if (s->d_acc) cudaFree(s->d_acc);
         if (s->h_acc) cudaFreeHost(s->h_acc);
     }
@@ -2108,7 +2138,71 @@ extern "C" int pir_server_answer_batch(pir_server* s, const pir_query* qs, uint3
 }
 
 extern "C" int pir_server_answer(pir_server* s, const pir_query* q, void* out, size_t out_len) {
-    return pir_server_answer_batch(s, q, 1, out, out_len);
+    if (!s || !q || !out) return fail(PIR_ERR_BAD_ARG, "null argument");
+    // The one-launch-per-shard path (see struct pir_server) when every shard can take it; anything else -- keyword
+    // queries, rows wider than 4 KB, the older kernels selected by an option -- goes through the batch path.
+    std::unique_lock<std::mutex> lk(s->mu);
+    const uint32_t W = q->group_size;
+    bool fast = s->h_ring_dev != nullptr && W != 0 && !q->is_keyword && !dev_phase_debug_on();
+    std::vector<QueryGeom> geoms(s->shards.size());
+    size_t live = 0;
+    for (size_t i = 0; i < s->shards.size() && fast; i++) {
+        if (query_geom(s->shards[i], q, &geoms[i]) != PIR_OK) fast = false;  // (the batch path reports the error)
+        else if (geoms[i].n_rows != 0) {
+            live++;
+            if (!single_launch_ok(s->shards[i], q, geoms[i]) || s->shards[i]->tune.signal_kernel) fast = false;
+        }
+    }
+    if (!fast || live == 0) {
+        lk.unlock();
+        return pir_server_answer_batch(s, q, 1, out, out_len);
+    }
+    const uint64_t row_bytes = (uint64_t)W * s->pitch;
+    const size_t ans = (size_t)W * s->slot_bytes;
+    if (out_len < ans) return fail(PIR_ERR_BAD_ARG, "out_len %zu < %zu", out_len, ans);
+    QueryConst qc;  // marshalled once, shared by all shards
+    int rc = build_query_const(q, geoms[0].nb, &qc);
+    if (rc) return rc;
+    s->ring_cv.wait(lk, [&] { return s->ring_busy != (1u << kHostRing) - 1u; });
+    uint32_t k = 0;
+    while ((s->ring_busy >> k) & 1u) k++;
+    s->ring_busy |= 1u << k;
+    uint8_t* d_slot = s->d_ring + (size_t)k * kAnswerMaxRowBytes;
+    uint8_t* h_slot = s->h_ring + (size_t)k * (kAnswerMaxRowBytes + 16);
+    uint8_t* h_slot_dev = s->h_ring_dev + (size_t)k * (kAnswerMaxRowBytes + 16);
+    uint32_t arrived = 0;  // shards whose arrival is (or will be) signalled
+    for (size_t i = 0; i < s->shards.size() && rc == PIR_OK; i++) {
+        if (geoms[i].n_rows == 0) continue;
+        pir_db* db = s->shards[i];
+        std::lock_guard<std::mutex> lkdb(db->mu);
+        DeviceGuard g(db->device);
+        bool signalled = false;
+        rc = enqueue_answer(db, q, geoms[i], d_slot, db->stream, /*zero_first=*/false, s->ring_arrivals(k), &signalled, false, nullptr, &qc);
+        if (rc == PIR_OK && signalled) arrived++;
+        else if (rc == PIR_OK) rc = fail(PIR_ERR_CUDA, "shard %zu did not take the one-launch path", i);
+    }
+    cudaError_t e = cudaSuccess;
+    {
+        DeviceGuard g(s->owner_device);
+        // (on a failure part-way the missing arrivals are made up for, so that the wait below ends and the slot is reset)
+        for (uint32_t m = arrived; m < live && e == cudaSuccess; m++) e = launch_signal_arrival(s->ring_arrivals(k), s->stream);
+        const uint64_t cycles = (uint64_t)(s->clock_khz > 0 ? s->clock_khz : 1000000) * 10000ull;  // 10 s
+        if (e == cudaSuccess)
+            e = launch_wait_read_reset(s->ring_arrivals(k), (uint32_t)live, cycles, (uint32_t*)d_slot, (uint32_t*)h_slot_dev,
+                                       (uint32_t*)(h_slot_dev + kAnswerMaxRowBytes), (uint32_t)(row_bytes / 4), s->stream);
+        if (e == cudaSuccess) e = cudaEventRecord(s->ring_ev[k], s->stream);
+    }
+    lk.unlock();
+    if (e == cudaSuccess) e = cudaEventSynchronize(s->ring_ev[k]);
+    if (e != cudaSuccess && rc == PIR_OK) rc = fail(PIR_ERR_CUDA, "pir_server_answer: %s", cudaGetErrorString(e));
+    if (rc == PIR_OK && *(volatile uint32_t*)(h_slot + kAnswerMaxRowBytes) != 0u)
+        rc = fail(PIR_ERR_CUDA, "timed out waiting for the shards' arrivals");
+    if (rc == PIR_OK)
+        for (uint32_t c = 0; c < W; c++) memcpy((uint8_t*)out + (size_t)c * s->slot_bytes, h_slot + (size_t)c * s->pitch, s->slot_bytes);
+    lk.lock();
+    s->ring_busy &= ~(1u << k);
+    s->ring_cv.notify_one();
+    return rc;
 }
 extern "C" int pir_debug_current_device(void) {  // (tests: no entry point may change the caller's current device)
     int d = -1;

@@ -206,3 +206,46 @@ def test_server_batch_two_phase_over_shards(gpu_lib):
         got = srv.answer_batch(qs)
     for i, p in enumerate(pairs):
         assert np.array_equal(got[i], oracle.answer(p[0][0], data, db_size, S)), i
+
+
+@pytest.mark.parametrize("n_shards,db_size,slot_bytes,W", [(3, 1 << 16, 256, 1), (8, 50000, 48, 2), (2, 1 << 15, 1024, 1)])
+def test_server_answer_from_many_threads(gpu_lib, n_shards, db_size, slot_bytes, W):
+    """pir_server_answer from 10 threads at once (more than the server's ring of 8 in-flight slots): one launch per
+    shard into a ring slot, one wait+read+reset launch on the owner, the server's mutex released while a caller waits.
+    Every answer must equal the oracle's, also when batch calls (the other path) run in between."""
+    import threading
+    data = oracle.synth_fill(61, 0, db_size, slot_bytes)
+    rows = db_size // W
+    rng = np.random.default_rng(n_shards)
+    pairs = [make_queries(6000 + k, db_size, W, int(rng.integers(0, rows))) for k in range(15)]
+    keys = [(p[0][s], p[1][s]) for p in pairs for s in (0, 1)]
+    want = [oracle.answer(o, data, db_size, slot_bytes, use_tree=True) for o, _ in keys]
+    errors = []
+    with sharding.Server(_devices(gpu_lib, n_shards), db_size, slot_bytes, shard_align=W) as srv:
+        srv.fill_synthetic(61)
+
+        def worker(t):
+            try:
+                for rep in range(3):
+                    for k in range(t, len(keys), 10):
+                        if not np.array_equal(srv.answer(keys[k][1]), want[k]):
+                            errors.append((t, rep, k))
+                    if t == 0:
+                        got = srv.answer_batch([keys[1][1], keys[2][1]])
+                        if not (np.array_equal(got[0], want[1]) and np.array_equal(got[1], want[2])):
+                            errors.append(("batch", rep))
+            except Exception as exc:   # noqa: BLE001
+                errors.append((t, repr(exc)))
+        ths = [threading.Thread(target=worker, args=(t,)) for t in range(10)]
+        for th in ths:
+            th.start()
+        for th in ths:
+            th.join(timeout=180)
+        assert not any(th.is_alive() for th in ths), "a thread hung"
+        # a wrong key is rejected and the ring keeps working
+        bad = _capi.PirQuery.from_bytes(keys[0][1].to_bytes())
+        bad.t_init = 9
+        with pytest.raises(_capi.PirError):
+            srv.answer(bad)
+        assert np.array_equal(srv.answer(keys[3][1]), want[3])
+    assert not errors, errors[:5]
