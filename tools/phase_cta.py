@@ -10,8 +10,9 @@ L = _capi.lib()
 n, S = 1 << 24, 256
 nb = L.pir_num_bits_for(n, 1, 0)
 par = int(sys.argv[1]) if len(sys.argv) > 1 else 0
+frac = int(sys.argv[2]) if len(sys.argv) > 2 else 1     # shard = the last 1/frac of the database
 h = C.c_void_p()
-_capi.check(L.pir_db_create(0, n, S, 0, n, C.byref(h)))
+_capi.check(L.pir_db_create(0, n, S, (frac - 1) * (n // frac), n // frac, C.byref(h)))
 _capi.check(L.pir_db_fill_synthetic(h, 3))
 keys = key_per_parity(L, nb, 12345)
 a0 = np.zeros(S, np.uint8)
