@@ -10,13 +10,12 @@ ring slot on rank 0's GPU (CUDA IPC mapping over NVLink; no NCCL in the data pat
             `steps` steps (all three listed in config.value_regions_ms); a region = `steps` single-query
             launches back to back on one stream per GPU (consecutive launches overlap as programmatic dependent
             launches; at N > 1 rank 0's event pair also covers the wait for the last query's N arrivals)
-  e2e       the same through the C ABI with HOST buffers, one query at a time: key in host memory -> answer in host
-            memory.  N = 1: pir_answer.  N > 1: the key lives in rank 0's host memory only and is fanned out to the
+  e2e       the same through the C ABI with HOST buffers and queries in flight (like `value`, which is back-to-back launches):
+            N = 1: pir_answer from 8 host threads on one handle; N > 1: the loop below with 4 queries in flight.
+  e2e_one_at_a_time  key in host memory -> answer in host memory, the next query only after the answer.  N = 1: pir_answer.  N > 1: the key lives in rank 0's host memory only and is fanned out to the
             other processes through a shared-memory mailbox; every rank launches its shard; rank 0 waits for the N
             arrivals, reads the combined answer and re-zeroes the ring slot (ring of 4) -- all inside the timed loop.
-            `e2e_pipelined` (N > 1): the same loop with 4 queries in flight.
             `e2e_single_process` times pir_server_answer (one process drives all N GPUs: the Go server's path).
-            `e2e_concurrent` (N = 1): pir_answer from 8 host threads at once on one handle (queries in flight overlap).
   roofline  dominant kernel vs measured HBM bandwidth on ALGORITHMIC bytes (rows x row_bytes per launch), plus the
             bound that binds: `lookup` = AES blocks/s against the AES-only rate of the same shard measured in this
             run (BITS-mode launches: same tree expansion, no row read), and `dram` = physical bytes (selected rows
@@ -630,7 +629,7 @@ def headline(env, args):
                                        "(programmatic dependent launch)" + ("" if world == 1 else
                                        "; rank 0's event pair ends after the device-side wait for the last query's %d arrivals; max over ranks" % world)},
             "queries_per_s": 1e3 / ms_step,
-            "e2e": {"value": db_bytes / (e2e_step * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": e2e_step,
+            "e2e_one_at_a_time": {"value": db_bytes / (e2e_step * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": e2e_step,
                     "h2d_bytes_per_step": C.sizeof(capi.PirQuery) * world, "d2h_bytes_per_step": S,
                     "queries_per_s": 1e3 / e2e_step,
                     "api": "pir_answer (C ABI, host key in / host answer out, one launch + one stream sync per query)" if world == 1 else
@@ -660,15 +659,23 @@ def headline(env, args):
         }
         if conc_ms is not None:
             per = conc_ms / (args.steps * CONC_PASSES)
-            line["e2e_concurrent"] = {"value": db_bytes / (per * 1e-3) / 1e9, "unit": UNIT, "ms_per_query": per, "queries_per_s": 1e3 / per,
-                                      "threads": CONC, "queries": args.steps * CONC_PASSES,
+            line["e2e"] = {"value": db_bytes / (per * 1e-3) / 1e9, "unit": UNIT, "ms_per_query": per, "queries_per_s": 1e3 / per,
+                                      "ms_per_step": per, "h2d_bytes_per_step": C.sizeof(capi.PirQuery), "d2h_bytes_per_step": S,
+                                      "in_flight": CONC, "threads": CONC, "queries": args.steps * CONC_PASSES,
+                                      "note": "throughput with queries in flight, like `value` (back-to-back launches); every query's key comes "
+                                              "from host memory and its answer goes to host memory inside the timed region; one query at a time: "
+                                              "e2e_one_at_a_time",
                                       "api": "pir_answer (host key in / host answer out) from %d host threads at once on ONE handle: each call "
                                              "enqueues under the handle's mutex and waits for its own event with the mutex released" % CONC}
         if pipe_ms is not None:
             per = pipe_ms / args.steps
-            line["e2e_pipelined"] = {"value": db_bytes / (per * 1e-3) / 1e9, "unit": UNIT, "ms_per_query": per, "queries_per_s": 1e3 / per,
+            line["e2e"] = {"value": db_bytes / (per * 1e-3) / 1e9, "unit": UNIT, "ms_per_query": per, "queries_per_s": 1e3 / per,
+                                     "ms_per_step": per, "h2d_bytes_per_step": C.sizeof(capi.PirQuery) * world, "d2h_bytes_per_step": S,
                                      "in_flight": PIPE_DEPTH,
-                                     "api": "as e2e (key fanned out from rank 0's host memory, pir_answer_accumulate_device on every rank, "
+                                     "note": "throughput with queries in flight, like `value` (back-to-back launches); every query's key comes "
+                                             "from rank 0's host memory and its combined answer goes to rank 0's host memory inside the timed "
+                                             "region; one query at a time: e2e_one_at_a_time",
+                                     "api": "as e2e_one_at_a_time (key fanned out from rank 0's host memory, pir_answer_accumulate_device on every rank, "
                                             "pir_combine_wait_read_reset on rank 0), with %d queries in flight: rank 0 collects answer k - %d "
                                             "after launching query k; combine ring of %d slots re-used inside the loop" % (
                                                 PIPE_DEPTH, PIPE_DEPTH - 1, PIPE_RING)}

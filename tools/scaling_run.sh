@@ -12,7 +12,7 @@ for N in ${NS:-1 2 4 8}; do
 import json
 try:
     d=json.loads(open('gpurun_out/${V}_scale_n$N.json').read().strip().splitlines()[-1]); r=d['roofline']
-    print('N=$N value',round(d['value']),'ms',round(d['ms_per_step'],4),'e2e',round(d['e2e']['value']),round(d['e2e']['ms_per_step'],4),'sp',d.get('e2e_single_process',{}).get('ms_per_step'),'iso',round(r['kernel_ms_isolated'],4),'aes',round(r['lookup']['aes_only_ms'],4),'checked',d['parity_checked'])
+    print('N=$N value',round(d['value']),'ms',round(d['ms_per_step'],4),'e2e',round(d['e2e']['value']),round(d['e2e']['ms_per_step'],4),'one-at-a-time',round(d['e2e_one_at_a_time']['value']),round(d['e2e_one_at_a_time']['ms_per_step'],4),'sp',d.get('e2e_single_process',{}).get('ms_per_step'),'iso',round(r['kernel_ms_isolated'],4),'aes',round(r['lookup']['aes_only_ms'],4),'checked',d['parity_checked'])
     for o in d.get('other_configs',[]): print('  ',o['config'], round(o['ms_per_step'],4), round(o['value'],1), o['parity_checked'])
 except Exception as e: print('parse failed',e)
 PY
