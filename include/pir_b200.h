@@ -110,7 +110,7 @@ int pir_db_device(const pir_db* db);
  *   top_warp (-1 = by row size, 0, 1)     the last scan warp walks the tops of the tasks ahead
  *   slice_log (0 = by task depth, 2, 3)   rows per thread per hand-off slice (log2)
  *   batch_mode (0 = by row size, 1 = one fused launch per query, 2 = bit vectors + one scan pass)
- *   batch_one_stream, batch_latency_split, host_copy_path, signal_kernel, serial_launch, no_lookahead, no_trim (0, 1)
+ *   batch_one_stream, batch_latency_split, host_copy_path, signal_kernel, serial_launch, no_lookahead, no_trim, direct_combine (0, 1)
  *   kernel_v1, expand_v1, keyword_v1, force_unfused (0, 1)   the older two-launch / per-row kernels
  * PIR_ERR_BAD_ARG for an unknown name or a value out of range.
  */

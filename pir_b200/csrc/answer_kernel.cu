@@ -1265,7 +1265,7 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
     if constexpr (NCB != 0) {  // (BITS mode has nothing to fold)
         __syncthreads();
         asm volatile("griddepcontrol.wait;" ::: "memory");
-        if (ap.arrivals) {  // (the slot may live on a peer GPU and several GPUs XOR into it: system scope)
+        if (ap.arrivals && !ap.final_out) {  // (the slot may live on a peer GPU and several GPUs XOR into it: system scope)
             for (uint32_t i = threadIdx.x; i < words_out; i += kAnswerThreads) {
                 const uint32_t v = red[i];
                 if (v) asm volatile("red.relaxed.sys.global.xor.b32 [%0], %1;" ::"l"(ap.out + i), "r"(v) : "memory");
@@ -1290,10 +1290,24 @@ answer_kernel(const __grid_constant__ QueryConst qc, const __grid_constant__ Ans
                 *flag = last ? 1u : 0u;
             }
             __syncthreads();
-            if (*flag) {
+            if (*flag && !ap.arrivals) {
                 __threadfence();
                 for (uint32_t i = threadIdx.x; i < words_out; i += kAnswerThreads) ap.final_out[i] = atomicExch(&ap.out[i], 0u);
                 __threadfence_system();
+            } else if (*flag) {
+                // Multi-GPU combine, folded: final_out is the combine slot (possibly on a peer GPU) that all shards XOR
+                // into.  Only this CTA pays the round trip: forward the shard's sum, then one thread fences with system
+                // scope (cumulative over the barrier) and publishes the arrival.
+                __threadfence();
+                for (uint32_t i = threadIdx.x; i < words_out; i += kAnswerThreads) {
+                    const uint32_t v = atomicExch(&ap.out[i], 0u);
+                    if (v) asm volatile("red.relaxed.sys.global.xor.b32 [%0], %1;" ::"l"(ap.final_out + i), "r"(v) : "memory");
+                }
+                __syncthreads();
+                if (threadIdx.x == 0) {
+                    asm volatile("fence.acq_rel.sys;" ::: "memory");
+                    asm volatile("red.release.sys.global.add.u32 [%0], 1;" ::"l"(ap.arrivals) : "memory");
+                }
             }
         } else if (ap.arrivals) {
             // Multi-GPU combine: this shard's partial is complete once every CTA's XORs are visible.  The CTA's

@@ -241,6 +241,7 @@ struct Tuning {
     bool serial_launch = false;   // no programmatic dependent launch between consecutive answer kernels
     bool no_lookahead = false;    // launches do not walk the next launch's tree top (kernels.cuh LaMail)
     bool no_trim = false;         // uniform tasks keep their full shape (147 CTAs on 2^24 rows instead of 148 trimmed ones)
+    bool direct_combine = false;  // multi-GPU: every CTA XORs into the (remote) combine slot itself, not only the launch's last CTA
 };
 
 constexpr uint32_t kCtaDoneRing = 64;
@@ -661,6 +662,7 @@ int set_tuning(Tuning& t, const char* name, int64_t v) {
         {"serial_launch", nullptr, &t.serial_launch, 0, 1},
         {"no_lookahead", nullptr, &t.no_lookahead, 0, 1},
         {"no_trim", nullptr, &t.no_trim, 0, 1},
+        {"direct_combine", nullptr, &t.direct_combine, 0, 1},
     };
     for (auto& e : tab) {
         if (strcmp(e.n, name)) continue;
@@ -861,6 +863,10 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
             db->acc_stream = st;
             ap.final_out = final_out;
             ap.cta_done = db->d_cta_done + (db->cta_done_next++ % kCtaDoneRing);
+            if (arrivals && signalled) {  // multi-GPU: the last CTA XORs the shard's sum into final_out (a combine slot) and signals
+                ap.arrivals = arrivals;
+                *signalled = true;
+            }
         } else if (arrivals && signalled && !db->tune.signal_kernel) {
             ap.arrivals = arrivals;
             ap.cta_done = db->d_cta_done + (db->cta_done_next++ % kCtaDoneRing);  // reset by the launch's last CTA
@@ -1767,9 +1773,15 @@ extern "C" int pir_answer_accumulate_device(pir_db* db, const pir_query* q, pir_
     if (geom.row_bytes > c->stride) return fail(PIR_ERR_BAD_ARG, "answer of %llu bytes exceeds the slot stride %zu",
                                                 (unsigned long long)geom.row_bytes, c->stride);
     bool signalled = false;
-    if ((rc = enqueue_answer(db, q, geom, c->base + (size_t)slot * c->stride, st, /*zero_first=*/false, c->arrivals(slot),
-                             &signalled)))
-        return rc;
+    uint8_t* d_slot = c->base + (size_t)slot * c->stride;
+    // The CTAs fold into the handle's local accumulator and the launch's LAST CTA forwards the shard's sum to the slot
+    // (possibly on a peer GPU) and signals: a CTA's exit does not wait for a round trip over NVLink, so the next launch's
+    // CTA gets the SM earlier.  (direct_combine: every CTA XORs into the slot itself, as in round 1.)
+    if (!db->tune.direct_combine && !db->tune.signal_kernel && single_launch_ok(db, q, geom))
+        rc = enqueue_answer(db, q, geom, db->d_acc, st, /*zero_first=*/false, c->arrivals(slot), &signalled, false, (uint32_t*)d_slot);
+    else
+        rc = enqueue_answer(db, q, geom, d_slot, st, /*zero_first=*/false, c->arrivals(slot), &signalled);
+    if (rc) return rc;
     if (!signalled) CU(launch_signal_arrival(c->arrivals(slot), st));
     return PIR_OK;
 }
@@ -2177,7 +2189,11 @@ extern "C" int pir_server_answer(pir_server* s, const pir_query* q, void* out, s
         std::lock_guard<std::mutex> lkdb(db->mu);
         DeviceGuard g(db->device);
         bool signalled = false;
-        rc = enqueue_answer(db, q, geoms[i], d_slot, db->stream, /*zero_first=*/false, s->ring_arrivals(k), &signalled, false, nullptr, &qc);
+        if (!db->tune.direct_combine)  // (fold locally, the launch's last CTA forwards: see pir_answer_accumulate_device)
+            rc = enqueue_answer(db, q, geoms[i], db->d_acc, db->stream, /*zero_first=*/false, s->ring_arrivals(k), &signalled, false,
+                                (uint32_t*)d_slot, &qc);
+        else
+            rc = enqueue_answer(db, q, geoms[i], d_slot, db->stream, /*zero_first=*/false, s->ring_arrivals(k), &signalled, false, nullptr, &qc);
         if (rc == PIR_OK && signalled) arrived++;
         else if (rc == PIR_OK) rc = fail(PIR_ERR_CUDA, "shard %zu did not take the one-launch path", i);
     }

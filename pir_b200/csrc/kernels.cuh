@@ -90,7 +90,8 @@ struct AnswerPlan {
     uint32_t* cta_done;
     // single-GPU call (optional): the launch's last CTA moves the finished answer from `out` to this buffer (device
     // memory or a mapped pinned host buffer) and leaves `out` zeroed for the next query -- no memset before and no
-    // copy after the kernel.  Needs cta_done; not combined with `arrivals`.
+    // copy after the kernel.  Needs cta_done.  With `arrivals` set as well, final_out is a multi-GPU combine slot: the last CTA
+    // XORs the shard's sum into it (system scope) and then bumps *arrivals.
     uint32_t* final_out;
     // look-ahead (optional, all null / 0 = off): this launch's sequence number on its handle, the hash of its shape,
     // the host-mapped mail ring [kLaMailRing] and the tops ring [kLaTopRing][gridDim.x] in device memory

@@ -75,13 +75,18 @@ def test_server_upload_routes_to_shards(gpu_lib):
         assert np.array_equal(srv.answer(q0), oracle.answer(o0, data, db_size, S))
 
 
-def test_combine_slots_single_process(gpu_lib):
-    """Two shard handles accumulate into ring slots of one combine buffer; the owner waits for both."""
+@pytest.mark.parametrize("direct", [0, 1])
+def test_combine_slots_single_process(gpu_lib, direct):
+    """Two shard handles accumulate into ring slots of one combine buffer; the owner waits for both.  direct = 0: the CTAs
+    fold into the handle's local accumulator and the launch's last CTA forwards the sum to the slot (shipped);
+    direct = 1: every CTA XORs into the slot itself (round 1)."""
     n, S = 1 << 13, 256
     data = oracle.synth_fill(9, 0, n, S)
     comb = sharding.Combine(0, 4, S)
     try:
         with Handle(n, S, 0, n // 2) as h0, Handle(n, S, n // 2, n // 2) as h1:
+            h0.set_option("direct_combine", direct)
+            h1.set_option("direct_combine", direct)
             h0.fill(9)
             h1.fill(9)
             for rep in range(2):  # second round re-uses the slots after a reset
@@ -222,6 +227,7 @@ def test_server_answer_from_many_threads(gpu_lib, n_shards, db_size, slot_bytes,
     want = [oracle.answer(o, data, db_size, slot_bytes, use_tree=True) for o, _ in keys]
     errors = []
     with sharding.Server(_devices(gpu_lib, n_shards), db_size, slot_bytes, shard_align=W) as srv:
+        srv.set_option("direct_combine", n_shards == 8)   # (both combine variants are covered)
         srv.fill_synthetic(61)
 
         def worker(t):
