@@ -175,4 +175,92 @@ __device__ __forceinline__ uint32_t leaf_parent_tail_even(const QueryConst& qc, 
     return leaf_select_bit(l0 ^ c0, l1 ^ c1, 0u, 0u) | (leaf_select_bit(sr0, sr1, 0u, 0u) << 1);
 }
 
+// ---- one child of a leaf parent (keyword_kernel.cu) --------------------------------------------------------
+// A keyword walk needs exactly ONE child of its deepest node, and of that child only the 8 seed bytes the selection bit is
+// computed from plus -- for keys with an odd FinalCW, or when the full Evaluate2P value is wanted -- its control bit:
+//   left  child: sL[0:8] = block 0 words 0,1;  tL = block 1 byte 0            152 (+145) lookups
+//   right child: sR[0:8] = block 1 bytes 1..8; tR = block 2 byte 1            153 (+133) lookups
+// against 458 for both children in full.  All lanes of the calling warp must want the same side (the caller batches).
+template <int NR>
+__device__ __forceinline__ void aes_block_rounds(const QueryConst& qc, int k, const uint32_t s[4], uint32_t lc, uint32_t a[4]) {
+#pragma unroll
+    for (int c = 0; c < 4; c++) a[c] = s[c] ^ qc.rk[k][c];
+#pragma unroll 3
+    for (int r = 1; r <= NR; r++) {
+        uint32_t n[4];
+        aes_round(a, n, &qc.rk[k][4 * r], lc);
+#pragma unroll
+        for (int c = 0; c < 4; c++) a[c] = n[c];
+    }
+}
+// two blocks side by side (two independent dependency chains): rounds 1..8 of blocks k0 and k1, then round 9 of k0 only if R9_BOTH is false
+template <bool R9_BOTH>
+__device__ __forceinline__ void aes_two_blocks(const QueryConst& qc, int k0, int k1, const uint32_t s[4], uint32_t lc, uint32_t a[4],
+                                               uint32_t b[4]) {
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        a[c] = s[c] ^ qc.rk[k0][c];
+        b[c] = s[c] ^ qc.rk[k1][c];
+    }
+#pragma unroll 2
+    for (int r = 1; r <= 8; r++) {
+        uint32_t n[4], m[4];
+        aes_round(a, n, &qc.rk[k0][4 * r], lc);
+        aes_round(b, m, &qc.rk[k1][4 * r], lc);
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            a[c] = n[c];
+            b[c] = m[c];
+        }
+    }
+    {
+        uint32_t n[4];
+        aes_round(a, n, &qc.rk[k0][36], lc);
+#pragma unroll
+        for (int c = 0; c < 4; c++) a[c] = n[c];
+    }
+    if (R9_BOTH) {
+        uint32_t m[4];
+        aes_round(b, m, &qc.rk[k1][36], lc);
+#pragma unroll
+        for (int c = 0; c < 4; c++) b[c] = m[c];
+    }
+}
+
+// (w0, w1) = the child's first 8 seed bytes, tc = its control bit (0 when need_t is false: the caller must not use it then)
+__device__ __forceinline__ void leaf_child_left(const QueryConst& qc, const uint32_t s[4], uint32_t t, uint32_t cw0, uint32_t cw1,
+                                                uint32_t cwtl, bool need_t, uint32_t lc, uint32_t& w0, uint32_t& w1, uint32_t& tc) {
+    const uint32_t m = 0u - t;
+    uint32_t a[4], b[4];
+    tc = 0u;
+    if (need_t) {
+        aes_two_blocks<true>(qc, 0, 1, s, lc, a, b);
+        const uint32_t r0 = sbox_b0(b[0], lc) ^ qc.rk[1][40] ^ s[0];  // byte 0 of block 1's output word 0
+        tc = (r0 & 1u) ^ (t & cwtl);
+    } else {
+        aes_block_rounds<9>(qc, 0, s, lc, a);
+    }
+    w0 = aes_last_word(a, 0, qc.rk[0][40], s[0], lc) ^ (cw0 & m);
+    w1 = aes_last_word(a, 1, qc.rk[0][41], s[1], lc) ^ (cw1 & m);
+}
+__device__ __forceinline__ void leaf_child_right(const QueryConst& qc, const uint32_t s[4], uint32_t t, uint32_t cw0, uint32_t cw1,
+                                                 uint32_t cwtr, bool need_t, uint32_t lc, uint32_t& w0, uint32_t& w1, uint32_t& tc) {
+    const uint32_t m = 0u - t;
+    uint32_t a[4], b[4];
+    tc = 0u;
+    if (need_t) {
+        aes_two_blocks<false>(qc, 1, 2, s, lc, a, b);  // block 1 after round 9, block 2 after round 8
+        const uint32_t n21 = aes_round_col(b, 1, qc.rk[2][37], lc);
+        const uint32_t b2 = sbox_b1(n21, lc) ^ qc.rk[2][40] ^ s[0];  // byte 1 of block 2's output word 0
+        tc = ((b2 >> 8) & 1u) ^ (t & cwtr);
+    } else {
+        aes_block_rounds<9>(qc, 1, s, lc, a);
+    }
+    const uint32_t r0 = aes_last_word(a, 0, qc.rk[1][40], s[0], lc);
+    const uint32_t r1 = aes_last_word(a, 1, qc.rk[1][41], s[1], lc);
+    const uint32_t r2 = sbox_b0(a[2], lc) ^ qc.rk[1][42] ^ s[2];      // byte 0 valid
+    w0 = __funnelshift_r(r0, r1, 8) ^ (cw0 & m);
+    w1 = __funnelshift_r(r1, r2, 8) ^ (cw1 & m);
+}
+
 }  // namespace pirb
