@@ -20,7 +20,10 @@
  *     thread-local human-readable message for the last failure on the calling thread.
  *   - the library never frees or keeps caller memory; outputs go to caller-allocated buffers.
  *   - a pir_db handle is bound to ONE CUDA device and owns a flat copy of (a shard of) the slots.
- *     Calls on one handle are serialised by an internal mutex; different handles are independent.
+ *     Every entry point is thread-safe.  Calls on one handle ENQUEUE under an internal mutex; single index queries
+ *     (pir_answer, pir_server_answer) then wait for their own completion event with the mutex released, so up to 8
+ *     queries of different threads are in flight on a handle and their kernels overlap on the GPU.  Batches, keyword
+ *     queries, expand / with-bits calls hold the mutex until they return.  Different handles are independent.
  *   - there is NO CPU fallback: without a usable CUDA device every compute entry point fails with
  *     PIR_ERR_CUDA.
  */
