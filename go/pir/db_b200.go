@@ -48,10 +48,28 @@ var GPUDevices = []int{0}
 var GPUShardAlign = 1
 
 type gpuDB struct {
-	mu      sync.Mutex
-	srv     *C.pir_server
+	mu      sync.RWMutex // lifetime of srv only: queries hold it for reading, ReleaseGPU for writing.  The C library is
+	srv     *C.pir_server //   thread-safe and keeps up to 8 single queries of different goroutines in flight per handle.
+	errMu   sync.Mutex
 	lastErr error // failure of a call whose signature has no error result (ExpandSharedQuery)
 }
+
+// takeErr returns and clears the error a call without an error result has left behind.
+func (g *gpuDB) takeErr() error {
+	g.errMu.Lock()
+	defer g.errMu.Unlock()
+	err := g.lastErr
+	g.lastErr = nil
+	return err
+}
+
+func (g *gpuDB) keepErr(err error) {
+	g.errMu.Lock()
+	g.lastErr = err
+	g.errMu.Unlock()
+}
+
+var errReleased = errors.New("pir_b200: the device copy of this Database was released")
 
 // keyed by the Database's ADDRESS (a uintptr does not keep the Database alive, so its finalizer can run; the finalizer
 // removes the entry before the address can be handed out again)
@@ -179,10 +197,12 @@ func (db *Database) PrivateSecretSharedQuery(query *QueryShare, nprocs int) (*Se
 	if err != nil {
 		return nil, err
 	}
-	g.mu.Lock()
-	defer g.mu.Unlock()
-	if g.lastErr != nil {
-		err, g.lastErr = g.lastErr, nil
+	g.mu.RLock()
+	defer g.mu.RUnlock()
+	if g.srv == nil {
+		return nil, errReleased
+	}
+	if err := g.takeErr(); err != nil {
 		return nil, err
 	}
 	out := make([]byte, query.GroupSize*db.SlotBytes)
@@ -200,10 +220,13 @@ func (db *Database) ExpandSharedQuery(query *QueryShare, nprocs int) []bool {
 		panic(err) // no handle to keep the error on; the reference panics on a bad AES key here too (dpf/server.go:29-31)
 	}
 	p, err := marshal(query)
-	g.mu.Lock()
-	defer g.mu.Unlock()
+	g.mu.RLock()
+	defer g.mu.RUnlock()
+	if err == nil && g.srv == nil {
+		err = errReleased
+	}
 	if err != nil {
-		g.lastErr = err
+		g.keepErr(err)
 		return nil
 	}
 	rows := db.DBSize / query.GroupSize // db.go:114: integer division before the Ceil
@@ -216,18 +239,18 @@ func (db *Database) ExpandSharedQuery(query *QueryShare, nprocs int) []bool {
 		var sh *C.pir_db
 		var first, n C.uint64_t
 		if err := cErr(C.pir_server_shard(g.srv, C.int(s), &sh)); err != nil {
-			g.lastErr = err
+			g.keepErr(err)
 			return nil
 		}
 		if err := cErr(C.pir_db_rows(sh, C.uint32_t(query.GroupSize), &first, &n)); err != nil {
-			g.lastErr = err
+			g.keepErr(err)
 			return nil
 		}
 		if n == 0 {
 			continue
 		}
 		if err := cErr(C.pir_expand_bits(sh, &p, (*C.uint8_t)(unsafe.Pointer(&raw[int(first)])), n)); err != nil {
-			g.lastErr = err
+			g.keepErr(err)
 			return nil
 		}
 	}
@@ -243,10 +266,12 @@ func (db *Database) PrivateSecretSharedQueryWithExpandedBits(query *QueryShare, 
 	if err != nil {
 		return nil, err
 	}
-	g.mu.Lock()
-	defer g.mu.Unlock()
-	if g.lastErr != nil {
-		err, g.lastErr = g.lastErr, nil
+	g.mu.RLock()
+	defer g.mu.RUnlock()
+	if g.srv == nil {
+		return nil, errReleased
+	}
+	if err := g.takeErr(); err != nil {
 		return nil, err
 	}
 	if bits == nil {
@@ -301,8 +326,11 @@ func (db *Database) PrivateSecretSharedQueryBatch(queries []*QueryShare) ([]*Sec
 			return nil, err
 		}
 	}
-	g.mu.Lock()
-	defer g.mu.Unlock()
+	g.mu.RLock()
+	defer g.mu.RUnlock()
+	if g.srv == nil {
+		return nil, errReleased
+	}
 	W := queries[0].GroupSize
 	out := make([]byte, len(queries)*W*db.SlotBytes)
 	if err := cErr(C.pir_server_answer_batch(g.srv, &ps[0], C.uint32_t(len(ps)), unsafe.Pointer(&out[0]), C.size_t(len(out)))); err != nil {
