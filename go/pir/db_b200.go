@@ -37,6 +37,8 @@ import (
 	"runtime"
 	"sync"
 	"unsafe"
+
+	"github.com/sachaservan/pir/dpf"
 )
 
 // GPUDevices lists the CUDA devices a Database is row-sharded over (SURVEY 8e: GPU g holds rows
@@ -341,4 +343,47 @@ func (db *Database) PrivateSecretSharedQueryBatch(queries []*QueryShare) ([]*Sec
 		res[i] = sharesFrom(out[i*W*db.SlotBytes:(i+1)*W*db.SlotBytes], W, db.SlotBytes)
 	}
 	return res, nil
+}
+
+// MarshalBinary / UnmarshalBinary (encoding.BinaryMarshaler / BinaryUnmarshaler): the reference keeps QueryShare in
+// process and has no serialisation (query.go:14-22); a client that sends its two shares to two servers uses the wire
+// layout of include/pir_b200.h (100 + 18*numBits bytes, little-endian) through pir_query_encode / pir_query_decode.
+func (q *QueryShare) MarshalBinary() ([]byte, error) {
+	p, err := marshal(q)
+	if err != nil {
+		return nil, err
+	}
+	buf := make([]byte, int(C.pir_query_wire_size(p.num_bits)))
+	if len(buf) == 0 {
+		return nil, errors.New("pir_b200: numBits out of range")
+	}
+	var n C.size_t
+	if err := cErr(C.pir_query_encode(&p, unsafe.Pointer(&buf[0]), C.size_t(len(buf)), &n)); err != nil {
+		return nil, err
+	}
+	return buf[:int(n)], nil
+}
+
+func (q *QueryShare) UnmarshalBinary(data []byte) error {
+	if len(data) == 0 {
+		return errors.New("pir_b200: empty encoded share")
+	}
+	var p C.pir_query
+	if err := cErr(C.pir_query_decode(unsafe.Pointer(&data[0]), C.size_t(len(data)), &p)); err != nil {
+		return err
+	}
+	nb := int(p.num_bits)
+	key := &dpf.Key2P{SInit: C.GoBytes(unsafe.Pointer(&p.s_init[0]), 16), TInit: byte(p.t_init), FinalCW: int(p.final_cw)}
+	key.CW = make([][]byte, nb)
+	for i := range key.CW {
+		key.CW[i] = C.GoBytes(unsafe.Pointer(&p.cw[i][0]), 18)
+	}
+	q.PrfKeys = make([]*dpf.PrfKey, C.PIR_NUM_PRF_KEYS)
+	for i := range q.PrfKeys {
+		q.PrfKeys[i] = &dpf.PrfKey{Bytes: C.GoBytes(unsafe.Pointer(&p.prf_keys[i][0]), 16)}
+	}
+	q.KeyTwoParty, q.KeyMultiParty = key, nil
+	q.IsKeywordBased, q.IsTwoParty = p.is_keyword != 0, p.is_two_party != 0
+	q.ShareNumber, q.GroupSize = uint(p.share_number), int(p.group_size)
+	return nil
 }

@@ -252,6 +252,28 @@ int pir_dpf_eval_points(int device, const pir_query* q, const uint64_t* xs, uint
 int pir_client_gen_two_server(uint32_t num_bits, uint64_t a, uint64_t b, const uint8_t* tape,
                               pir_query* q0, pir_query* q1);
 
+/* ---- wire encoding of a query share (host only) ------------------------------------------------ */
+/* The reference has no serialisation for QueryShare / Key2P (query.go:14-22, dpf/common.go:30-35 are in-process structs),
+ * yet the two servers receive their shares over a network.  pir_query above is the in-memory form (1336 bytes, host
+ * endianness); this is the compact, endianness-defined form: 100 + 18*num_bits bytes, every integer little-endian:
+ *   0  "PIRQ"            4   magic
+ *   4  version           1   PIR_WIRE_VERSION
+ *   5  flags             1   bit0 share_number, bit1 is_keyword, bit2 t_init, bit3 is_two_party; bits 4-7 zero
+ *   6  num_bits          1   1..PIR_MAX_NUM_BITS
+ *   7  zero              1
+ *   8  group_size        4
+ *  12  final_cw          8   two's complement
+ *  20  s_init           16
+ *  36  prf_keys         64   4 x 16 (dpf/common.go:10 ships four)
+ * 100  cw               18 * num_bits
+ * decode rejects anything else (wrong magic/version/length, non-zero padding, num_bits out of range) with PIR_ERR_BAD_KEY
+ * and leaves *q zeroed; a decoded share is exactly what encode was given (fields beyond num_bits in cw are zero). */
+#define PIR_WIRE_VERSION 1
+#define PIR_WIRE_HEADER_BYTES 100
+size_t pir_query_wire_size(uint32_t num_bits);  /* 0 if num_bits is out of range */
+int    pir_query_encode(const pir_query* q, void* buf, size_t buf_len, size_t* written);
+int    pir_query_decode(const void* buf, size_t len, pir_query* q);
+
 /* ---- host helpers ----------------------------------------------------------------------------- */
 /* acc[i] ^= part[i]: XorSlots (slot.go:19-30) / Recover (query.go:278-297) / multi-GPU combine. */
 void pir_xor_combine(void* acc, const void* part, size_t len);

@@ -31,6 +31,7 @@ EXPORTS = [
     "pir_answer", "pir_answer_batch", "pir_expand_bits", "pir_expand_bits_noalloc", "pir_answer_with_bits",
     "pir_answer_batch_device", "pir_dpf_eval_points", "pir_xor_combine", "pir_num_bits_for",
     "pir_kernel_launch_count", "pir_client_gen_two_server",
+    "pir_query_wire_size", "pir_query_encode", "pir_query_decode",
     "pir_db_set_kernel_timing", "pir_db_get_kernel_timing", "pir_db_time_expansion",
     "pir_combine_wait_read_reset", "pir_combine_wait_device",
     "pir_server_create", "pir_server_destroy", "pir_server_num_shards", "pir_server_shard",
@@ -139,6 +140,10 @@ def lib():
     L.pir_num_bits_for.argtypes = [C.c_uint64, C.c_uint32, C.c_int]
     L.pir_num_bits_for.restype = C.c_uint32
     L.pir_kernel_launch_count.restype = C.c_uint64
+    L.pir_query_wire_size.argtypes = [C.c_uint32]
+    L.pir_query_wire_size.restype = C.c_size_t
+    L.pir_query_encode.argtypes = [qp, vp, C.c_size_t, C.POINTER(C.c_size_t)]
+    L.pir_query_decode.argtypes = [vp, C.c_size_t, qp]
     L.pir_client_gen_two_server.argtypes = [C.c_uint32, C.c_uint64, C.c_uint64, u8p, qp, qp]
     L.pir_db_set_kernel_timing.argtypes = [vp, C.c_int]
     L.pir_db_get_kernel_timing.argtypes = [vp, C.POINTER(C.c_double), u64p]

@@ -196,6 +196,63 @@ extern "C" void pir_xor_combine(void* acc, const void* part, size_t len) {
     for (size_t i = 0; i < len; i++) a[i] ^= b[i];
 }
 
+// ---- wire encoding of a query share (layout in include/pir_b200.h) --------------------------------
+extern "C" size_t pir_query_wire_size(uint32_t num_bits) {
+    if (num_bits == 0 || num_bits > PIR_MAX_NUM_BITS) return 0;
+    return (size_t)PIR_WIRE_HEADER_BYTES + (size_t)PIR_CW_BYTES * num_bits;
+}
+
+extern "C" int pir_query_encode(const pir_query* q, void* buf, size_t buf_len, size_t* written) {
+    if (written) *written = 0;
+    if (!q || !buf) return fail(PIR_ERR_BAD_ARG, "null argument");
+    const size_t need = pir_query_wire_size(q->num_bits);
+    if (!need) return fail(PIR_ERR_BAD_KEY, "num_bits %u out of range", q->num_bits);
+    if (q->t_init > 1 || q->share_number > 1 || q->is_keyword > 1 || q->is_two_party > 1 || q->reserved)
+        return fail(PIR_ERR_BAD_KEY, "flag fields must be 0 or 1 and reserved must be 0");
+    if (buf_len < need) return fail(PIR_ERR_BAD_ARG, "buffer of %zu bytes, %zu needed", buf_len, need);
+    uint8_t* b = (uint8_t*)buf;
+    memcpy(b, "PIRQ", 4);
+    b[4] = PIR_WIRE_VERSION;
+    b[5] = (uint8_t)(q->share_number | (q->is_keyword << 1) | (q->t_init << 2) | (q->is_two_party << 3));
+    b[6] = (uint8_t)q->num_bits;
+    b[7] = 0;
+    for (int k = 0; k < 4; k++) b[8 + k] = (uint8_t)(q->group_size >> (8 * k));
+    const uint64_t f = (uint64_t)q->final_cw;
+    for (int k = 0; k < 8; k++) b[12 + k] = (uint8_t)(f >> (8 * k));
+    memcpy(b + 20, q->s_init, 16);
+    memcpy(b + 36, q->prf_keys, 64);
+    memcpy(b + PIR_WIRE_HEADER_BYTES, q->cw, (size_t)PIR_CW_BYTES * q->num_bits);
+    if (written) *written = need;
+    return PIR_OK;
+}
+
+extern "C" int pir_query_decode(const void* buf, size_t len, pir_query* q) {
+    if (!q) return fail(PIR_ERR_BAD_ARG, "null argument");
+    memset(q, 0, sizeof(*q));
+    if (!buf) return fail(PIR_ERR_BAD_ARG, "null argument");
+    const uint8_t* b = (const uint8_t*)buf;
+    if (len < PIR_WIRE_HEADER_BYTES) return fail(PIR_ERR_BAD_KEY, "encoded share of %zu bytes is shorter than its header", len);
+    if (memcmp(b, "PIRQ", 4) != 0) return fail(PIR_ERR_BAD_KEY, "not an encoded query share (magic)");
+    if (b[4] != PIR_WIRE_VERSION) return fail(PIR_ERR_BAD_KEY, "wire version %u, this library reads %u", b[4], PIR_WIRE_VERSION);
+    if ((b[5] & 0xF0) || b[7]) return fail(PIR_ERR_BAD_KEY, "non-zero padding in an encoded share");
+    const size_t need = pir_query_wire_size(b[6]);
+    if (!need) return fail(PIR_ERR_BAD_KEY, "num_bits %u out of range", b[6]);
+    if (len != need) return fail(PIR_ERR_BAD_KEY, "encoded share of %zu bytes, %zu expected for num_bits %u", len, need, b[6]);
+    q->share_number = b[5] & 1;
+    q->is_keyword = (b[5] >> 1) & 1;
+    q->t_init = (b[5] >> 2) & 1;
+    q->is_two_party = (b[5] >> 3) & 1;
+    q->num_bits = b[6];
+    uint64_t f = 0;
+    for (int k = 0; k < 4; k++) q->group_size |= (uint32_t)b[8 + k] << (8 * k);
+    for (int k = 0; k < 8; k++) f |= (uint64_t)b[12 + k] << (8 * k);
+    q->final_cw = (int64_t)f;
+    memcpy(q->s_init, b + 20, 16);
+    memcpy(q->prf_keys, b + 36, 64);
+    memcpy(q->cw, b + PIR_WIRE_HEADER_BYTES, (size_t)PIR_CW_BYTES * q->num_bits);
+    return PIR_OK;
+}
+
 // ---- query marshalling --------------------------------------------------------------------------
 static int build_query_const(const pir_query* q, uint32_t num_bits, QueryConst* qc) {
     if (!q) return fail(PIR_ERR_BAD_ARG, "query is null");

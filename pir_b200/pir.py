@@ -93,6 +93,31 @@ class QueryShare:
         return dpf.pod_from_parts(self.PrfKeys, self.KeyTwoParty, self.ShareNumber, num_bits,
                                   group_size=self.GroupSize, is_keyword=self.IsKeywordBased)
 
+    # The reference keeps shares in process and has no serialisation; these two carry Go's encoding.BinaryMarshaler /
+    # BinaryUnmarshaler names and use the wire layout of include/pir_b200.h (pir_query_encode / pir_query_decode).
+    def MarshalBinary(self):
+        L = _capi.lib()
+        q = self.to_pod()
+        buf = (C.c_uint8 * L.pir_query_wire_size(q.num_bits))()
+        n = C.c_size_t()
+        _capi.check(L.pir_query_encode(C.byref(q), buf, len(buf), C.byref(n)))
+        return bytes(buf[:n.value])
+
+    @classmethod
+    def UnmarshalBinary(cls, data):
+        L = _capi.lib()
+        q = _capi.PirQuery()
+        raw = (C.c_uint8 * max(len(data), 1)).from_buffer_copy(bytes(data) or b"\0")
+        _capi.check(L.pir_query_decode(raw, len(data), C.byref(q)))
+        s = cls()
+        s.PrfKeys = [dpf.PrfKey(bytes(q.prf_keys[i])) for i in range(dpf.initPRFLen)]
+        s.KeyTwoParty = dpf.Key2P(bytes(q.s_init), q.t_init, [bytes(q.cw[i]) for i in range(q.num_bits)], q.final_cw)
+        s.IsKeywordBased = bool(q.is_keyword)
+        s.IsTwoParty = bool(q.is_two_party)
+        s.ShareNumber = q.share_number
+        s.GroupSize = q.group_size
+        return s
+
 
 class DBMetadata:
     """db.go:15-18 and the client-side query constructors of query.go:42-101."""

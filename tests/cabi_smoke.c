@@ -39,6 +39,20 @@ int main(void) {
         fprintf(stderr, "generated key differs from the golden key\n");
         return 5;
     }
+    /* the shares travel to their servers in the wire encoding; each server answers the DECODED share */
+    for (int s = 0; s < 2; s++) {
+        uint8_t wire[PIR_WIRE_HEADER_BYTES + PIR_CW_BYTES * PIR_MAX_NUM_BITS];
+        size_t n = 0;
+        pir_query back;
+        CHECK(pir_query_encode(&q[s], wire, sizeof wire, &n));
+        if (n != pir_query_wire_size(G_NUM_BITS)) return 8;
+        CHECK(pir_query_decode(wire, n, &back));
+        if (memcmp(&back, &q[s], sizeof(pir_query)) != 0) {
+            fprintf(stderr, "decoded share differs from the encoded one\n");
+            return 8;
+        }
+        q[s] = back;
+    }
     /* server: Database{Slots} -> device handle, then PrivateSecretSharedQuery for both shares (db.go:68-72) */
     CHECK(pir_db_create(0, G_DB_SIZE, G_SLOT_BYTES, 0, G_DB_SIZE, &db));
     CHECK(pir_db_upload(db, 0, G_DB, G_DB_SIZE));

@@ -185,3 +185,92 @@ def test_work_split_chooser_is_valid_for_typical_shards():
                     assert (n + rows_per_task - 1) // rows_per_task <= sms
             if logn == 24:
                 assert hiw.value == 12 and d.value == 7 - (frac.bit_length() - 1)
+
+
+# ---- wire encoding of a query share (include/pir_b200.h: pir_query_wire_size / _encode / _decode) ----------------
+def _encode(L, q):
+    buf = (C.c_uint8 * L.pir_query_wire_size(q.num_bits))()
+    n = C.c_size_t()
+    _capi.check(L.pir_query_encode(C.byref(q), buf, len(buf), C.byref(n)))
+    assert n.value == len(buf) == 100 + 18 * q.num_bits
+    return bytes(buf)
+
+
+def _decode(L, data):
+    q = _capi.PirQuery()
+    raw = (C.c_uint8 * max(len(data), 1)).from_buffer_copy(bytes(data) or b"\0")
+    _capi.check(L.pir_query_decode(raw, len(data), C.byref(q)))
+    return q
+
+
+@pytest.mark.parametrize("case", GOLDEN["pir"] + GOLDEN["dpf"], ids=lambda c: c["name"])
+def test_wire_encoding_round_trips_every_golden_share(case):
+    L = _capi.lib()
+    for key in ("query0", "query1"):
+        q = _capi.PirQuery.from_buffer_copy(bytes.fromhex(case[key]))
+        wire = _encode(L, q)
+        # the layout is the documented one, byte for byte, written here independently of the C code
+        want = b"PIRQ" + bytes([1, q.share_number | q.is_keyword << 1 | q.t_init << 2 | q.is_two_party << 3, q.num_bits, 0])
+        want += int(q.group_size).to_bytes(4, "little") + int(q.final_cw).to_bytes(8, "little", signed=True)
+        want += bytes(q.s_init) + b"".join(bytes(q.prf_keys[i]) for i in range(4))
+        want += b"".join(bytes(q.cw[i]) for i in range(q.num_bits))
+        assert wire == want
+        assert _decode(L, wire).to_bytes() == q.to_bytes()
+
+
+def test_wire_encoding_covers_every_field_and_size():
+    L = _capi.lib()
+    rng = np.random.default_rng(77)
+    assert L.pir_query_wire_size(0) == 0 and L.pir_query_wire_size(65) == 0
+    for nb in (1, 17, 25, 29, 32, 64):
+        q = _capi.PirQuery()
+        C.memmove(C.byref(q), rng.integers(0, 256, size=C.sizeof(q), dtype=np.uint8).tobytes(), C.sizeof(q))
+        q.t_init, q.share_number, q.is_keyword, q.is_two_party = int(rng.integers(2)), int(rng.integers(2)), int(rng.integers(2)), 1
+        q.num_bits, q.reserved = nb, 0
+        q.final_cw = int(rng.integers(-2**63, 2**63 - 1))
+        for i in range(nb, 64):                      # correction words beyond num_bits are not part of the share
+            C.memset(q.cw[i], 0, 18)
+        assert L.pir_query_wire_size(nb) == 100 + 18 * nb
+        assert _decode(L, _encode(L, q)).to_bytes() == q.to_bytes()
+
+
+def test_wire_decoding_rejects_malformed_input():
+    L = _capi.lib()
+    q0, q1 = _capi.PirQuery(), _capi.PirQuery()
+    _capi.check(L.pir_client_gen_two_server(17, 41000, 1, None, C.byref(q0), C.byref(q1)))
+    good = _encode(L, q1)
+    bad = {
+        "empty": b"", "short header": good[:99], "truncated": good[:-1], "trailing byte": good + b"\0",
+        "magic": b"QRIP" + good[4:], "version": good[:4] + b"\x02" + good[5:], "flag padding": good[:5] + bytes([good[5] | 0x10]) + good[6:],
+        "pad byte": good[:7] + b"\x01" + good[8:], "num_bits 0": good[:6] + b"\x00" + good[7:], "num_bits 65": good[:6] + b"\x41" + good[7:],
+        "num_bits vs length": good[:6] + b"\x12" + good[7:],
+    }
+    for name, data in bad.items():
+        q = _capi.PirQuery()
+        C.memset(C.byref(q), 0xEE, C.sizeof(q))
+        raw = (C.c_uint8 * max(len(data), 1)).from_buffer_copy(data or b"\0")
+        assert L.pir_query_decode(raw, len(data), C.byref(q)) == _capi.PIR_ERR_BAD_KEY, name
+        assert L.pir_last_error()
+        assert q.to_bytes() == bytes(C.sizeof(q)), name        # nothing half-decoded is left behind
+    # encode: a buffer one byte short, flag fields out of range
+    buf = (C.c_uint8 * (len(good) - 1))()
+    n = C.c_size_t(5)
+    assert L.pir_query_encode(C.byref(q1), buf, len(buf), C.byref(n)) == _capi.PIR_ERR_BAD_ARG and n.value == 0
+    q1.t_init = 2
+    buf = (C.c_uint8 * len(good))()
+    assert L.pir_query_encode(C.byref(q1), buf, len(buf), None) == _capi.PIR_ERR_BAD_KEY
+
+
+def test_query_share_marshal_binary_mirror():
+    """pir.QueryShare.MarshalBinary / UnmarshalBinary: the share a server decodes evaluates like the one the client made."""
+    from pir_b200 import pir
+    md = pir.DBMetadata(SlotBytes=32, DBSize=3000)
+    for shares in (md.NewIndexQueryShares(1234, 2, 2), md.NewKeywordQueryShares(99, 1, 2)):
+        for s in shares:
+            wire = s.MarshalBinary()
+            back = pir.QueryShare.UnmarshalBinary(wire)
+            assert back.to_pod().to_bytes() == s.to_pod().to_bytes()
+            assert (back.GroupSize, back.IsKeywordBased, back.ShareNumber) == (s.GroupSize, s.IsKeywordBased, s.ShareNumber)
+            assert back.MarshalBinary() == wire
+    with pytest.raises(_capi.PirError):
+        pir.QueryShare.UnmarshalBinary(b"not a share")
