@@ -102,6 +102,11 @@ int pir_db_download(pir_db* db, uint64_t slot_index, void* host_slots, uint64_t 
 int pir_db_fill_synthetic(pir_db* db, uint64_t seed);
 /* Keywords for the shard's slots (Database.SetKeywords, db.go:392-394): n must equal slot_count. */
 int pir_db_set_keywords(pir_db* db, const uint64_t* keywords, uint64_t n);
+/* Keyword queries with group size W > 1 evaluate Keywords[r] at ROW r (db.go:132-135), and on every shard but the first
+ * r = slot / W lies below the shard's own slots: row_keywords[k] = Keywords[first_row + k] for the n = n_rows rows that
+ * pir_db_rows(db, group_size) reports.  One group size at a time (a new call replaces the last); not needed on an
+ * unsharded handle; pir_server_set_keywords calls it on every shard for the server's shard_align. */
+int pir_db_set_row_keywords(pir_db* db, uint32_t group_size, const uint64_t* row_keywords, uint64_t n);
 uint32_t pir_db_slot_pitch(const pir_db* db);
 int pir_db_device(const pir_db* db);
 /*
@@ -182,7 +187,8 @@ int pir_server_shard(pir_server* s, int i, pir_db** db);
 int pir_server_upload(pir_server* s, uint64_t slot_index, const void* host_slots, uint64_t n_slots);
 int pir_server_fill_synthetic(pir_server* s, uint64_t seed);
 /* Database.SetKeywords (db.go:392-394) for the whole database: n must equal db_size; shard g keeps
- * keywords[slot_begin_g, +slot_count_g).  Keyword queries (db.go:119-121,132-135) need group_size 1 here. */
+ * keywords[slot_begin_g, +slot_count_g) and, when shard_align > 1, the keywords of its rows at that group size
+ * (pir_db_set_row_keywords).  Keyword queries (db.go:119-121,132-135) take group_size 1 or shard_align. */
 int pir_server_set_keywords(pir_server* s, const uint64_t* keywords, uint64_t n);
 /* pir_db_set_option on every shard. */
 int pir_server_set_option(pir_server* s, const char* name, int64_t value);

@@ -27,7 +27,7 @@ PIR_ERR_UNSUPPORTED = -5
 EXPORTS = [
     "pir_abi_version", "pir_last_error", "pir_device_count",
     "pir_db_create", "pir_db_destroy", "pir_db_upload", "pir_db_download", "pir_db_fill_synthetic",
-    "pir_db_set_keywords", "pir_db_slot_pitch", "pir_db_device", "pir_db_rows", "pir_db_set_option",
+    "pir_db_set_keywords", "pir_db_set_row_keywords", "pir_db_slot_pitch", "pir_db_device", "pir_db_rows", "pir_db_set_option",
     "pir_answer", "pir_answer_batch", "pir_expand_bits", "pir_expand_bits_noalloc", "pir_answer_with_bits",
     "pir_answer_batch_device", "pir_dpf_eval_points", "pir_xor_combine", "pir_num_bits_for",
     "pir_kernel_launch_count", "pir_client_gen_two_server",
@@ -127,6 +127,7 @@ def lib():
     L.pir_db_device.argtypes = [vp]
     L.pir_db_rows.argtypes = [vp, C.c_uint32, u64p, u64p]
     L.pir_db_set_option.argtypes = [vp, C.c_char_p, C.c_int64]
+    L.pir_db_set_row_keywords.argtypes = [vp, C.c_uint32, u64p, C.c_uint64]
     L.pir_server_set_option.argtypes = [vp, C.c_char_p, C.c_int64]
     L.pir_answer.argtypes = [vp, qp, vp, C.c_size_t]
     L.pir_answer_batch.argtypes = [vp, qp, C.c_uint32, vp, C.c_size_t]

@@ -314,6 +314,11 @@ struct pir_db {
     uint64_t slot_begin = 0, slot_count = 0;
     uint8_t* d_slots = nullptr;
     uint64_t* d_keywords = nullptr;
+    // keyword queries with group size W > 1 on a shard: row r evaluates Keywords[r] (db.go:132-135), and r = slot / W lies
+    // below the shard's own slots.  pir_db_set_row_keywords keeps the keywords of the shard's ROWS for one W.
+    uint64_t* d_row_keywords = nullptr;
+    uint32_t rowkw_w = 0;
+    uint64_t rowkw_first = 0, rowkw_n = 0;
     cudaStream_t stream = nullptr;
     std::mutex mu;
     Tuning tune;
@@ -669,6 +674,7 @@ extern "C" int pir_db_destroy(pir_db* db) {
     if (db->d_out) cudaFree(db->d_out);
     if (db->h_out) cudaFreeHost(db->h_out);
     if (db->d_keywords) cudaFree(db->d_keywords);
+    if (db->d_row_keywords) cudaFree(db->d_row_keywords);
     if (db->d_slots) cudaFree(db->d_slots);
     for (auto& ev : db->ev_pool) {
         cudaEventDestroy(ev.first);
@@ -807,6 +813,28 @@ extern "C" int pir_db_set_keywords(pir_db* db, const uint64_t* keywords, uint64_
     return PIR_OK;
 }
 
+extern "C" int pir_db_set_row_keywords(pir_db* db, uint32_t group_size, const uint64_t* row_keywords, uint64_t n) {
+    if (!db || (!row_keywords && n)) return fail(PIR_ERR_BAD_ARG, "null argument");
+    uint64_t first = 0, rows = 0;
+    int rc = shard_rows(db, group_size, &first, &rows);
+    if (rc) return rc;
+    if (n != rows) return fail(PIR_ERR_BAD_ARG, "expected %llu keywords (one per row of the shard at group size %u), got %llu",
+                               (unsigned long long)rows, group_size, (unsigned long long)n);
+    std::lock_guard<std::mutex> lk(db->mu);
+    DeviceGuard g(db->device);
+    CU(cudaStreamSynchronize(db->stream));
+    if (db->d_row_keywords) cudaFree(db->d_row_keywords);
+    db->d_row_keywords = nullptr;
+    db->rowkw_w = 0;
+    CU(cudaMalloc(&db->d_row_keywords, (n ? n : 1) * sizeof(uint64_t)));
+    CU(cudaMemcpy(db->d_row_keywords, row_keywords, n * sizeof(uint64_t), cudaMemcpyHostToDevice));
+    CU(cudaStreamSynchronize(0));  // (see pir_db_upload)
+    db->rowkw_w = group_size;
+    db->rowkw_first = first;
+    db->rowkw_n = n;
+    return PIR_OK;
+}
+
 extern "C" int pir_db_rows(const pir_db* db, uint32_t group_size, uint64_t* first_row, uint64_t* n_rows) {
     if (!db || !first_row || !n_rows) return fail(PIR_ERR_BAD_ARG, "null argument");
     return shard_rows(db, group_size, first_row, n_rows);
@@ -822,6 +850,25 @@ struct QueryGeom {
 };
 
 void fill_answer_split(pir_db* db, const QueryGeom& g, AnswerPlan* ap, bool throughput = false);
+
+// The keywords of the rows [g.first_row, g.first_row + g.n_rows) a keyword query evaluates on this handle (db.go:132-135:
+// row r uses Keywords[r]).  With group size 1, and on an unsharded handle or a server's first shard, they are among the
+// handle's per-slot keywords; a later shard queried with W > 1 needs the per-row copy of pir_db_set_row_keywords.
+int shard_keywords(const pir_db* db, const QueryGeom& g, const uint64_t** kw) {
+    if (!db->d_keywords) return fail(PIR_ERR_BAD_ARG, "keyword query on a database without keywords (pir_db_set_keywords)");
+    if (g.first_row >= db->slot_begin && g.first_row + g.n_rows <= db->slot_begin + db->slot_count) {
+        *kw = db->d_keywords + (g.first_row - db->slot_begin);
+        return PIR_OK;
+    }
+    if (db->d_row_keywords && db->rowkw_w == g.W && db->rowkw_first == g.first_row && db->rowkw_n == g.n_rows) {
+        *kw = db->d_row_keywords;
+        return PIR_OK;
+    }
+    return fail(PIR_ERR_BAD_ARG,
+                "keyword query with group_size %u on a shard that holds slots [%llu, %llu): its rows' keywords lie outside the shard; "
+                "give them with pir_db_set_row_keywords (pir_server_set_keywords does, for the server's shard_align)",
+                g.W, (unsigned long long)db->slot_begin, (unsigned long long)(db->slot_begin + db->slot_count));
+}
 
 int query_geom(const pir_db* db, const pir_query* q, QueryGeom* g) {
 #ifdef PIRB_DEV
@@ -862,10 +909,8 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
     const QueryConst& qc = prebuilt ? *prebuilt : qc_local;  // (a multi-shard server marshals every key once, not once per shard)
     const DeviceCtx& ctx = *db->ctx;
     if (q->is_keyword) {
-        if (!db->d_keywords) return fail(PIR_ERR_BAD_ARG, "keyword query on a database without keywords (pir_db_set_keywords)");
-        if (g.first_row < db->slot_begin || g.first_row + g.n_rows > db->slot_begin + db->slot_count)
-            return fail(PIR_ERR_BAD_ARG, "keyword queries with group_size > 1 need an unsharded handle");
-        // keyword queries need group size 1 on a shard (checked above), so row r of the shard is slot slot_begin + r
+        const uint64_t* kw = nullptr;
+        if ((rc = shard_keywords(db, g, &kw))) return rc;
         const uint8_t* rows0 = db->d_slots + (g.first_row * g.W - db->slot_begin) * (uint64_t)db->pitch;
         if (!db->tune.keyword_v1 && !db->tune.force_unfused && keyword_fused_supports(g.row_bytes)) {
             // one kernel: prefix-sharing walk with the row XOR fused in (no byte-per-row bit vector through HBM)
@@ -881,17 +926,17 @@ int enqueue_answer(pir_db* db, const pir_query* q, const QueryGeom& g, uint8_t* 
                 db->ev_used++;
                 CU(cudaEventRecord(e0, st));
             }
-            CU(launch_keyword_walk(qc, db->d_keywords + (g.first_row - db->slot_begin), 0, g.n_rows, nullptr, nullptr, ctx.d_t0,
+            CU(launch_keyword_walk(qc, kw, 0, g.n_rows, nullptr, nullptr, ctx.d_t0,
                                    ctx.smem_base, ctx.num_sms, st, rows0, g.row_bytes, (uint32_t*)d_out));
             if (e1) CU(cudaEventRecord(e1, st));
             return PIR_OK;
         }
         if ((rc = ensure_bits(db, g.n_rows))) return rc;
         if (db->tune.keyword_v1)
-            CU(launch_eval_points(qc, db->d_keywords + (g.first_row - db->slot_begin), 0, g.n_rows, nullptr,
+            CU(launch_eval_points(qc, kw, 0, g.n_rows, nullptr,
                                   db->d_bits, ctx.d_t0, ctx.smem_base, st));
         else
-            CU(launch_keyword_walk(qc, db->d_keywords + (g.first_row - db->slot_begin), 0, g.n_rows, nullptr,
+            CU(launch_keyword_walk(qc, kw, 0, g.n_rows, nullptr,
                                    db->d_bits, ctx.d_t0, ctx.smem_base, ctx.num_sms, st));
         CU(launch_scan_bytes(rows0, g.row_bytes, g.n_rows, db->d_bits, (uint32_t*)d_out, ctx.num_sms, st));
         return PIR_OK;
@@ -1303,14 +1348,13 @@ extern "C" int pir_expand_bits(pir_db* db, const pir_query* q, uint8_t* bits_out
     if ((rc = ensure_bits(db, n_rows))) return rc;
     const DeviceCtx& ctx = *db->ctx;
     if (q->is_keyword) {
-        if (!db->d_keywords) return fail(PIR_ERR_BAD_ARG, "keyword query on a database without keywords");
-        if (geom.first_row < db->slot_begin || geom.first_row + geom.n_rows > db->slot_begin + db->slot_count)
-            return fail(PIR_ERR_BAD_ARG, "keyword queries with group_size > 1 need an unsharded handle");
+        const uint64_t* kw = nullptr;
+        if ((rc = shard_keywords(db, geom, &kw))) return rc;
         if (db->tune.keyword_v1)
-            CU(launch_eval_points(qc, db->d_keywords + (geom.first_row - db->slot_begin), 0, n_rows, nullptr,
+            CU(launch_eval_points(qc, kw, 0, n_rows, nullptr,
                                   db->d_bits, ctx.d_t0, ctx.smem_base, db->stream));
         else
-            CU(launch_keyword_walk(qc, db->d_keywords + (geom.first_row - db->slot_begin), 0, n_rows, nullptr,
+            CU(launch_keyword_walk(qc, kw, 0, n_rows, nullptr,
                                    db->d_bits, ctx.d_t0, ctx.smem_base, ctx.num_sms, db->stream));
     } else if (!db->tune.expand_v1) {
         // answer kernel in BITS mode (packed bit vector, no rows read), then one byte per row
@@ -1923,6 +1967,7 @@ struct pir_server {
     int owner_device = 0;
     uint64_t db_size = 0;
     uint32_t slot_bytes = 0, pitch = 0;
+    uint32_t shard_align = 1;
     uint8_t* d_acc = nullptr;        // on the owner device; peers reach it over NVLink (peer access)
     uint64_t acc_cap = 0;
     uint8_t* h_acc = nullptr;        // pinned
@@ -1972,6 +2017,7 @@ extern "C" int pir_server_create(const int* devices, int n_devices, uint64_t db_
     s->slot_bytes = slot_bytes;
     s->pitch = (slot_bytes + 15u) & ~15u;
     s->owner_device = devices[0];
+    s->shard_align = shard_align;
     const uint64_t units = db_size / shard_align;  // whole alignment units; the ragged tail goes to the last shard
     int rc = PIR_OK;
     for (int i = 0; i < n_devices && rc == PIR_OK; i++) {
@@ -2105,6 +2151,13 @@ extern "C" int pir_server_set_keywords(pir_server* s, const uint64_t* keywords, 
     for (pir_db* db : s->shards) {  // every shard keeps the keywords of its own slots only
         int rc = pir_db_set_keywords(db, keywords + db->slot_begin, db->slot_count);
         if (rc) return rc;
+        // ... and, for keyword queries at the group size the shards are aligned to, those of its own ROWS: row r evaluates
+        // Keywords[r] (db.go:132-135), which for W > 1 belongs to an earlier shard's slots
+        if (s->shard_align > 1) {
+            uint64_t first = 0, rows = 0;
+            if ((rc = pir_db_rows(db, s->shard_align, &first, &rows))) return rc;
+            if ((rc = pir_db_set_row_keywords(db, s->shard_align, keywords + first, rows))) return rc;
+        }
     }
     return PIR_OK;
 }
@@ -2144,8 +2197,12 @@ extern "C" int pir_server_answer_batch(pir_server* s, const pir_query* qs, uint3
             if (i == 0 && (rc = build_query_const(&qs[k], geom.nb, &qcs[k]))) return rc;
             if (geom.nb != geoms[0].nb) return fail(PIR_ERR_BAD_ARG, "shards disagree on the domain size");
         }
-        if (qs[0].is_keyword && geoms[i].n_rows && !s->shards[i]->d_keywords)
-            return fail(PIR_ERR_BAD_ARG, "keyword query on a database without keywords (pir_server_set_keywords)");
+        if (qs[0].is_keyword && geoms[i].n_rows) {  // (nothing has been enqueued yet)
+            const uint64_t* kw = nullptr;
+            if (!s->shards[i]->d_keywords)
+                return fail(PIR_ERR_BAD_ARG, "keyword query on a database without keywords (pir_server_set_keywords)");
+            if ((rc = shard_keywords(s->shards[i], geoms[i], &kw))) return rc;
+        }
     }
     {
         DeviceGuard g(s->owner_device);

@@ -57,6 +57,10 @@ class Handle:
         kw = np.ascontiguousarray(kw, dtype=np.uint64)
         _capi.check(self.L.pir_db_set_keywords(self.h, kw.ctypes.data_as(C.POINTER(C.c_uint64)), kw.size))
 
+    def set_row_keywords(self, group_size, kw):
+        kw = np.ascontiguousarray(kw, dtype=np.uint64)
+        _capi.check(self.L.pir_db_set_row_keywords(self.h, group_size, kw.ctypes.data_as(C.POINTER(C.c_uint64)), kw.size))
+
     def rows(self, group_size):
         a, b = C.c_uint64(), C.c_uint64()
         _capi.check(self.L.pir_db_rows(self.h, group_size, C.byref(a), C.byref(b)))

@@ -64,6 +64,69 @@ def test_server_keyword_query_over_shards(gpu_lib, n_shards, db_size, slot_bytes
         assert np.array_equal(a0 ^ a1, data[target])
 
 
+@pytest.mark.parametrize("n_shards,db_size,slot_bytes,W", [(2, 4096, 32, 2), (3, 5001, 48, 3), (8, 1 << 14, 32, 4), (4, 900, 272, 2)])
+def test_server_keyword_query_with_a_group_size_over_shards(gpu_lib, n_shards, db_size, slot_bytes, W):
+    """Keyword query with GroupSize > 1 on a row-sharded database: row r evaluates Keywords[r] (db.go:132-135), which for every
+    shard but the first is a keyword of an EARLIER shard's slots -- pir_server_set_keywords hands each shard its rows' keywords."""
+    rng = np.random.default_rng(23)
+    data = rng.integers(0, 256, size=(db_size, slot_bytes), dtype=np.uint8)
+    kws = np.sort(rng.choice(1 << 32, size=db_size, replace=False).astype(np.uint64))
+    rows = db_size // W
+    for target in (rows - 1, (rows * 5) // 7, 0):
+        (o0, o1), (q0, q1) = make_queries(14, db_size, W, target, is_keyword=True, keyword=int(kws[target]))
+        with sharding.Server(_devices(gpu_lib, n_shards), db_size, slot_bytes, shard_align=W) as srv:
+            srv.upload(data)
+            srv.set_keywords(kws)
+            a0, a1 = srv.answer(q0), srv.answer(q1)
+            assert np.array_equal(a0, oracle.answer(o0, data, db_size, slot_bytes, keywords=kws))
+            assert np.array_equal(a1, oracle.answer(o1, data, db_size, slot_bytes, keywords=kws))
+            assert np.array_equal(a0 ^ a1, data[target * W:(target + 1) * W].reshape(-1))
+            both = srv.answer_batch([q1, q0])
+            assert np.array_equal(both[0], a1) and np.array_equal(both[1], a0)
+            if target == 0 and n_shards > 1:
+                # group size 1 still works on the same server; another group size that divides the shards does not have its
+                # rows' keywords on the later shards and says so
+                (p0, _), (g0, _) = make_queries(15, db_size, 1, db_size - 1, is_keyword=True, keyword=int(kws[db_size - 1]))
+                assert np.array_equal(srv.answer(g0), oracle.answer(p0, data, db_size, slot_bytes, keywords=kws))
+                if W == 4:
+                    (_, _), (h0, _) = make_queries(16, db_size, 2, 5, is_keyword=True, keyword=int(kws[5]))
+                    with pytest.raises(_capi.PirError) as e:
+                        srv.answer(h0)
+                    assert "pir_db_set_row_keywords" in str(e.value)
+
+
+def test_shard_handle_row_keywords(gpu_lib):
+    """pir_db_set_row_keywords on a bare shard handle: ExpandSharedQuery of a keyword query with GroupSize 3 on the middle
+    shard equals the oracle's bits for those rows; without the row keywords the call fails with a clear error."""
+    rng = np.random.default_rng(29)
+    db_size, S, W = 3000, 64, 3
+    kws = np.sort(rng.choice(1 << 32, size=db_size, replace=False).astype(np.uint64))
+    (o0, _), (q0, _) = make_queries(17, db_size, W, 444, is_keyword=True, keyword=int(kws[444]))
+    with Handle(db_size, S, slot_begin=999, slot_count=1002) as h:
+        h.fill(3)
+        h.set_keywords(kws[999:999 + 1002])
+        r0, n = h.rows(W)
+        assert (r0, n) == (333, 334)
+        with pytest.raises(_capi.PirError) as e:
+            h.expand_bits(q0)
+        assert "pir_db_set_row_keywords" in str(e.value)
+        with pytest.raises(_capi.PirError):
+            h.set_row_keywords(W, kws[r0:r0 + n - 1])           # one keyword per row of the shard
+        h.set_row_keywords(W, kws[r0:r0 + n])
+        want = oracle.expand_shared_query(o0, db_size, keywords=kws, row_begin=r0, n_rows=n)
+        assert np.array_equal(h.expand_bits(q0), want) and want[444 - r0] != oracle.expand_shared_query(
+            make_queries(17, db_size, W, 444, is_keyword=True, keyword=int(kws[444]))[0][1], db_size, keywords=kws, row_begin=r0, n_rows=n)[444 - r0]
+        data = oracle.synth_fill(3, 0, db_size, S)
+        part = np.zeros(W * S, dtype=np.uint8)
+        for r in np.nonzero(want)[0]:
+            part ^= data[(r0 + r) * W:(r0 + r + 1) * W].reshape(-1)
+        assert np.array_equal(h.answer(q0), part)
+        # a different group size replaces the copy
+        h.set_row_keywords(1, kws[999:999 + 1002])
+        with pytest.raises(_capi.PirError):
+            h.expand_bits(q0)
+
+
 def test_server_upload_routes_to_shards(gpu_lib):
     rng = np.random.default_rng(3)
     db_size, S = 1000, 48
