@@ -5,6 +5,8 @@ import ctypes as C, os, sys, time
 import numpy as np
 sys.path.insert(0, os.getcwd())
 from pir_b200 import _capi
+if os.environ.get("DEV_SO"):
+    _capi.DEV_LIB_PATH = os.path.abspath(os.environ["DEV_SO"])   # A/B of two builds
 _capi.use_dev_library()   # PIRB_* switches and phase counters exist in the -DPIRB_DEV build only
 L = _capi.lib()
 n, S, Q = 1 << int(os.environ.get("LOG_ROWS", "22")), int(os.environ.get("SLOT", "1024")), int(os.environ.get("Q", "64"))
