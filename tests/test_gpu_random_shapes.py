@@ -120,3 +120,40 @@ def test_random_row_sharded_servers_match_the_oracle(gpu_lib, seed):
             both = srv.answer_batch([q for q, _ in answers])
             for j, (_, a) in enumerate(answers):
                 assert np.array_equal(both[j], a), tag
+
+
+@pytest.mark.parametrize("seed", range(24))
+def test_random_medium_size_shards_match_the_oracle(gpu_lib, seed):
+    """Sizes at which the answer kernel splits the tree over all CTAs in every way it knows (2^18 to 2^23.5 rows, up to 3 GiB):
+    index queries on random shard windows, bits against the oracle's tree expansion and answers against its row XOR over the
+    synthetic database, both shares, single calls and a batch."""
+    rng = np.random.default_rng(9000 + seed)
+    for k in range(3):
+        slot_bytes = int(rng.choice([16, 32, 48, 100, 256, 336, 512, 1024]))
+        W = int(rng.choice([1, 1, 2, 3]))
+        rows = int(2 ** rng.uniform(18, 23.5))
+        rows = min(rows, (3 << 30) // (slot_bytes * W))
+        db_size = rows * W + int(rng.integers(0, W))                 # a ragged tail now and then
+        r0 = int(rng.integers(0, rows // 2)) if rng.integers(0, 2) else 0
+        cnt = int(rng.integers(rows // 4, rows - r0 + 1))
+        to_end = r0 + cnt == rows
+        opt = OPTIONS[int(rng.integers(0, len(OPTIONS)))]
+        fill_seed, key_seed = int(rng.integers(1, 1 << 30)), int(rng.integers(1, 1 << 30))
+        tag = "seed %d case %d: db_size %d slot_bytes %d W %d rows [%d, +%d) option %r" % (seed, k, db_size, slot_bytes, W, r0, cnt, opt)
+        with Handle(db_size, slot_bytes, slot_begin=r0 * W, slot_count=db_size - r0 * W if to_end else cnt * W) as h:
+            h.fill(fill_seed)
+            if opt:
+                h.set_option(*opt)
+            assert h.rows(W) == (r0, cnt), tag
+            idx = r0 + int(rng.integers(0, cnt))
+            (o0, o1), (q0, q1) = make_queries(key_seed, db_size, W, idx)
+            bits = [oracle.expand_tree(o, db_size, row_begin=r0, n_rows=cnt, nthreads=8) for o in (o0, o1)]
+            want = oracle.answers_over_synth(fill_seed, slot_bytes, W, bits, row_begin=r0, nthreads=8)
+            got = [h.answer(q0), h.answer(q1)]
+            for s, q in enumerate((q0, q1)):
+                assert np.array_equal(h.expand_bits(q), bits[s]), tag
+                assert np.array_equal(got[s], want[s]), tag
+            assert np.array_equal(got[0] ^ got[1], oracle.synth_fill(fill_seed, idx * W, W, slot_bytes).reshape(-1)), tag
+            both = h.answer_batch([q1, q0, q0, q1])
+            for j, s in enumerate((1, 0, 0, 1)):
+                assert np.array_equal(both[j], want[s]), tag
