@@ -157,3 +157,36 @@ def test_random_medium_size_shards_match_the_oracle(gpu_lib, seed):
             both = h.answer_batch([q1, q0, q0, q1])
             for j, s in enumerate((1, 0, 0, 1)):
                 assert np.array_equal(both[j], want[s]), tag
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_arbitrary_key_bytes_evaluate_like_the_reference(gpu_lib, seed):
+    """A share arrives from the network: whatever bytes it holds (PRF keys, seed, correction words with arbitrary tLCW / tRCW
+    bytes, FinalCW), the server must compute what dpf/server.go:55-101 computes on them -- not only on keys an honest client
+    minted.  Every field at random (flag fields within their ranges), index and keyword mode, against the oracle."""
+    import ctypes as C
+    from pir_b200 import _capi
+    from tests.helpers import eval_points
+    rng = np.random.default_rng(7000 + seed)
+    for k in range(4):
+        keyword = bool(k & 1)
+        db_size, S, W = int(rng.integers(1, 40000)), int(rng.choice([16, 40, 256])), int(rng.choice([1, 2]))
+        W = min(W, db_size)
+        nb = oracle.num_bits_for(db_size, W, keyword)
+        raw = bytearray(rng.integers(0, 256, size=C.sizeof(_capi.PirQuery), dtype=np.uint8).tobytes())
+        q = _capi.PirQuery.from_buffer(raw)
+        q.t_init, q.share_number, q.is_keyword, q.is_two_party = int(rng.integers(2)), int(rng.integers(2)), int(keyword), 1
+        q.num_bits, q.group_size, q.reserved = nb, W, 0
+        o = oracle.query_from_bytes(bytes(raw))
+        tag = "seed %d case %d: db_size %d slot_bytes %d W %d keyword %r" % (seed, k, db_size, S, W, keyword)
+        kws = rng.integers(0, 1 << 32, size=db_size, dtype=np.uint64) if keyword else None     # (duplicates allowed)
+        xs = rng.integers(0, 1 << min(nb, 62), size=500, dtype=np.uint64)
+        assert np.array_equal(eval_points(q, xs), oracle.evaluate2p(o, xs)), tag
+        with Handle(db_size, S) as h:
+            h.fill(9 + k)
+            if keyword:
+                h.set_keywords(kws)
+            bits = oracle.expand_shared_query(o, db_size, keywords=kws)
+            assert np.array_equal(h.expand_bits(q), bits), tag
+            data = oracle.synth_fill(9 + k, 0, db_size, S)
+            assert np.array_equal(h.answer(q), oracle.answer(o, data, db_size, S, keywords=kws)), tag
